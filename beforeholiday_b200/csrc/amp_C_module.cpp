@@ -1,0 +1,267 @@
+// amp_C_module.cpp -- the `amp_C` Python extension: a thin torch/pybind11 adaptor over the C ABI in
+// include/mt_b200.h.  It keeps the exact operator names and positional signatures of the reference module
+// (/root/reference/csrc/amp_C_frontend.cpp:165-194) so that apex.optimizers.* / amp's LossScaler / user code
+// calling amp_C.multi_tensor_*(chunk_size, noop_flag, tensor_lists, ...) run unchanged.
+//
+// What lives here: argument validation with the reference's error messages
+// (/root/reference/csrc/multi_tensor_apply.cuh:53-72), flattening of list[list[Tensor]] into MtTensorLists,
+// allocation of return / scratch tensors through torch's caching allocator (stream-ordered, capture-safe),
+// and translation of error codes into RuntimeError.  No arithmetic happens here.
+#include <torch/extension.h>
+
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+
+#include <tuple>
+#include <vector>
+
+#include "../../include/mt_b200.h"
+
+namespace {
+
+using TensorLists = std::vector<std::vector<at::Tensor>>;
+
+int dtype_tag(at::ScalarType t, const char* who) {
+    switch (t) {
+        case at::ScalarType::Float: return MT_F32;
+        case at::ScalarType::Half: return MT_F16;
+        case at::ScalarType::BFloat16: return MT_BF16;
+        case at::ScalarType::Double: return MT_F64;
+        default: TORCH_CHECK(false, who, ": unsupported dtype ", t);
+    }
+    return -1;
+}
+
+struct Flat {
+    MtTensorLists tl{};
+    std::vector<const void*> ptrs;
+    std::vector<int64_t> numel;
+    std::vector<at::Tensor> keep;  // densified sparse inputs
+    c10::DeviceIndex device = 0;
+    cudaStream_t stream = nullptr;
+};
+
+// Validation + flattening.  Same checks, same messages as multi_tensor_apply<depth>().
+void flatten(const TensorLists& lists, size_t depth_lo, size_t depth_hi, const char* who, Flat& f) {
+    TORCH_CHECK(lists.size() >= depth_lo && lists.size() <= depth_hi, "tensor_lists.size() != depth");
+    const size_t depth = lists.size();
+    const size_t len0 = lists[0].size();
+    TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
+    auto ref_device = lists[0][0].device();
+    TORCH_CHECK(ref_device.type() == at::kCUDA, "expected input to be on cuda");
+    f.ptrs.resize(depth * len0);
+    f.numel.resize(len0);
+    for (size_t l = 0; l < depth; l++) {
+        TORCH_CHECK(lists[l].size() == len0, "Size mismatch among tensor lists");
+        const auto st0 = lists[l][0].scalar_type();
+        for (size_t t = 0; t < len0; t++) {
+            const at::Tensor& x = lists[l][t];
+            bool contiguous_memory = x.is_sparse() ? x._values().is_contiguous() : x.is_contiguous();
+            contiguous_memory = contiguous_memory || x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
+                                x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
+            TORCH_CHECK(contiguous_memory, "A tensor was not contiguous.");
+            TORCH_CHECK(x.device() == ref_device, "A tensor was not on the same device as the first tensor");
+            TORCH_CHECK(x.numel() == lists[0][t].numel(), "Size mismatch");
+            // The reference dispatches on element [0] of each list and reinterprets the rest; a mixed list is a
+            // silent misread there.  Here it is an error.
+            TORCH_CHECK(x.scalar_type() == st0, who, ": all tensors of one list must share a dtype");
+            if (x.is_sparse()) {  // densify, as multi_tensor_apply.cuh:92-95
+                at::Tensor dst = at::zeros(x.sizes(), x.options().layout(at::kStrided));
+                dst.add_(x);
+                f.keep.push_back(dst);
+                f.ptrs[l * len0 + t] = dst.data_ptr();
+            } else {
+                f.ptrs[l * len0 + t] = x.data_ptr();
+            }
+            if (l == 0) f.numel[t] = x.numel();
+        }
+        f.tl.dtype[l] = dtype_tag(st0, who);
+    }
+    f.device = ref_device.index();
+    f.tl.depth = (int32_t)depth;
+    f.tl.device = (int32_t)f.device;
+    f.tl.ntensors = (int64_t)len0;
+    f.tl.ptrs = f.ptrs.data();
+    f.tl.numel = f.numel.data();
+    f.stream = at::cuda::getCurrentCUDAStream(f.device).stream();
+}
+
+int32_t* flag_ptr(const at::Tensor& noop_flag) {
+    TORCH_CHECK(noop_flag.is_cuda() && noop_flag.scalar_type() == at::ScalarType::Int && noop_flag.numel() >= 1,
+                "noop_flag must be a CUDA int32 tensor with at least one element");
+    return noop_flag.data_ptr<int32_t>();
+}
+
+void check(int rc) { TORCH_CHECK(rc == MT_OK, mt_last_error()); }
+
+// ---------------------------------------------------------------------------------------------------
+void multi_tensor_scale(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, float scale) {
+    Flat f;
+    flatten(tensor_lists, 2, 2, "multi_tensor_scale", f);
+    check(mt_multi_tensor_scale(chunk_size, flag_ptr(noop_flag), &f.tl, scale, f.stream));
+}
+
+void multi_tensor_axpby(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, float a, float b,
+                        int arg_to_check) {
+    Flat f;
+    flatten(tensor_lists, 3, 3, "multi_tensor_axpby", f);
+    check(mt_multi_tensor_axpby(chunk_size, flag_ptr(noop_flag), &f.tl, a, b, arg_to_check, f.stream));
+}
+
+std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_flag, const TensorLists& tensor_lists,
+                                               bool with_scale, float scale, at::optional<bool> per_tensor_python) {
+    const bool per_tensor = per_tensor_python.has_value() ? per_tensor_python.value() : false;
+    Flat f;
+    flatten(tensor_lists, with_scale ? 2 : 1, with_scale ? 2 : 1, with_scale ? "multi_tensor_l2norm_scale" : "multi_tensor_l2norm", f);
+    const c10::cuda::CUDAGuard guard(f.device);
+    auto fopt = tensor_lists[0][0].options().dtype(at::kFloat).layout(at::kStrided);
+    at::Tensor ret = at::empty({1}, fopt);
+    at::Tensor ret_per_tensor = at::empty({per_tensor ? (int64_t)f.tl.ntensors : 0}, fopt);
+    const size_t sbytes = mt_norm_scratch_bytes(chunk_size, &f.tl);
+    at::Tensor scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)}, fopt.dtype(at::kByte));
+    int rc;
+    if (with_scale)
+        rc = mt_multi_tensor_l2norm_scale(chunk_size, flag_ptr(noop_flag), &f.tl, scale, per_tensor,
+                                          ret.data_ptr<float>(), per_tensor ? ret_per_tensor.data_ptr<float>() : nullptr,
+                                          scratch.data_ptr(), sbytes, f.stream);
+    else
+        rc = mt_multi_tensor_l2norm(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor, ret.data_ptr<float>(),
+                                    per_tensor ? ret_per_tensor.data_ptr<float>() : nullptr, scratch.data_ptr(), sbytes,
+                                    f.stream);
+    check(rc);
+    return std::make_tuple(ret, ret_per_tensor);
+}
+
+std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                                       at::optional<bool> per_tensor_python) {
+    return l2norm_impl(chunk_size, noop_flag, tensor_lists, false, 0.f, per_tensor_python);
+}
+
+std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm_scale(int chunk_size, at::Tensor noop_flag,
+                                                             TensorLists tensor_lists, float scale,
+                                                             at::optional<bool> per_tensor_python) {
+    return l2norm_impl(chunk_size, noop_flag, tensor_lists, true, scale, per_tensor_python);
+}
+
+void multi_tensor_adam(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
+                       const float beta1, const float beta2, const float epsilon, const int step, const int mode,
+                       const int bias_correction, const float weight_decay) {
+    Flat f;
+    flatten(tensor_lists, 4, 4, "multi_tensor_adam", f);
+    check(mt_multi_tensor_adam(chunk_size, flag_ptr(noop_flag), &f.tl, lr, beta1, beta2, epsilon, step, mode,
+                               bias_correction, weight_decay, f.stream));
+}
+
+void multi_tensor_sgd(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, float wd, float momentum,
+                      float dampening, float lr, bool nesterov, bool first_run, bool wd_after_momentum, float scale) {
+    Flat f;
+    flatten(tensor_lists, 3, 4, "multi_tensor_sgd", f);
+    if (tensor_lists.size() == 4)
+        for (const auto& t : tensor_lists[3])
+            TORCH_CHECK(t.scalar_type() == at::ScalarType::Half, "Additional output tensors should always be fp16.");
+    TORCH_CHECK(noop_flag.device() == tensor_lists[0][0].device(),
+                "expected noop flag to be on the same device as tensors");
+    check(mt_multi_tensor_sgd(chunk_size, flag_ptr(noop_flag), &f.tl, wd, momentum, dampening, lr, nesterov, first_run,
+                              wd_after_momentum, scale, f.stream));
+}
+
+void multi_tensor_lamb(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
+                       const float beta1, const float beta2, const float epsilon, const int step,
+                       const int bias_correction, const float weight_decay, const int grad_averaging, const int mode,
+                       at::Tensor global_grad_norm, const float max_grad_norm, at::optional<bool> use_nvlamb_python) {
+    const bool use_nvlamb = use_nvlamb_python.has_value() ? use_nvlamb_python.value() : false;
+    Flat f;
+    flatten(tensor_lists, 4, 4, "multi_tensor_lamb", f);
+    TORCH_CHECK(global_grad_norm.is_cuda() && global_grad_norm.scalar_type() == at::ScalarType::Float,
+                "global_grad_norm must be a CUDA float tensor");
+    const c10::cuda::CUDAGuard guard(f.device);
+    const size_t sbytes = mt_lamb_scratch_bytes(chunk_size, &f.tl);
+    at::Tensor scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)},
+                                   tensor_lists[0][0].options().dtype(at::kByte).layout(at::kStrided));
+    check(mt_multi_tensor_lamb(chunk_size, flag_ptr(noop_flag), &f.tl, lr, beta1, beta2, epsilon, step, bias_correction,
+                               weight_decay, grad_averaging, mode, global_grad_norm.data_ptr<float>(), max_grad_norm,
+                               use_nvlamb, scratch.data_ptr(), sbytes, f.stream));
+}
+
+void multi_tensor_lamb_stage1_cuda(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                   at::Tensor per_tensor_decay, const int step, const float beta1, const float beta2,
+                                   const float epsilon, at::Tensor global_grad_norm,
+                                   const float max_global_grad_norm) {
+    Flat f;
+    flatten(tensor_lists, 5, 5, "multi_tensor_lamb_stage1_cuda", f);
+    // The reference dereferences the norm pointer on the host (csrc/multi_tensor_lamb_stage_1.cu:126-127), i.e. it
+    // only works for a host-readable tensor; .item() accepts both host and device tensors.
+    const float gnorm = global_grad_norm.item<float>();
+    check(mt_multi_tensor_lamb_stage1(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_decay.data_ptr<float>(), step,
+                                      beta1, beta2, epsilon, gnorm, max_global_grad_norm, f.stream));
+}
+
+void multi_tensor_lamb_stage2_cuda(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                   at::Tensor per_tensor_param_norm, at::Tensor per_tensor_update_norm, const float lr,
+                                   const float weight_decay, at::optional<bool> use_nvlamb_python) {
+    const bool use_nvlamb = use_nvlamb_python.has_value() ? use_nvlamb_python.value() : false;
+    Flat f;
+    flatten(tensor_lists, 2, 2, "multi_tensor_lamb_stage2_cuda", f);
+    check(mt_multi_tensor_lamb_stage2(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_param_norm.data_ptr<float>(),
+                                      per_tensor_update_norm.data_ptr<float>(), lr, weight_decay, use_nvlamb, f.stream));
+}
+
+// distributed_adam_cuda.multi_tensor_fused_adam
+// (/root/reference/apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp:3-19) plus a trailing
+// `honour_noop` (default false = reference behaviour).
+void multi_tensor_fused_adam(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                             at::Tensor per_tensor_beta1, at::Tensor per_tensor_beta2,
+                             at::Tensor per_tensor_bias_correction, at::Tensor per_tensor_eps,
+                             at::Tensor per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
+                             bool honour_noop) {
+    Flat f;
+    TORCH_CHECK(tensor_lists.size() == 4 || tensor_lists.size() == 5, "expected tensor lists of size 4 or 5");
+    flatten(tensor_lists, 4, 5, "multi_tensor_fused_adam", f);
+    const int64_t n = f.tl.ntensors;
+    TORCH_CHECK(per_tensor_beta1.numel() >= n && per_tensor_beta2.numel() >= n && per_tensor_bias_correction.numel() >= n &&
+                    per_tensor_eps.numel() >= n && per_tensor_weight_decay.numel() >= n,
+                "per-tensor hyper-parameter tensors are shorter than the tensor lists");
+    TORCH_CHECK(per_tensor_bias_correction.scalar_type() == at::ScalarType::Int, "per_tensor_bias_correction must be int32");
+    check(mt_multi_tensor_fused_adam(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(),
+                                     per_tensor_beta2.data_ptr<float>(), per_tensor_bias_correction.data_ptr<int32_t>(),
+                                     per_tensor_eps.data_ptr<float>(), per_tensor_weight_decay.data_ptr<float>(), lr,
+                                     grad_scale, step, mode, honour_noop ? 1 : 0, f.stream));
+}
+
+py::dict table_cache_stats(int device) {
+    MtCacheStats s{};
+    check(mt_table_cache_stats(device, &s));
+    py::dict d;
+    d["hits"] = s.hits;
+    d["misses"] = s.misses;
+    d["uploads_bytes"] = s.uploads_bytes;
+    d["entries"] = s.entries;
+    d["device_bytes"] = s.device_bytes;
+    return d;
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    m.doc() = "B200-native amp_C: multi-tensor-apply optimizer path over libmt_b200.so";
+    m.def("multi_tensor_scale", &multi_tensor_scale, "Fused overflow check + scale for a list of contiguous tensors");
+    m.def("multi_tensor_sgd", &multi_tensor_sgd, "Fused SGD optimizer for list of contiguous tensors");
+    m.def("multi_tensor_axpby", &multi_tensor_axpby, "out = a*x + b*y for a list of contiguous tensors");
+    m.def("multi_tensor_l2norm", &multi_tensor_l2norm, "Computes L2 norm for a list of contiguous tensors");
+    m.def("multi_tensor_l2norm_scale", &multi_tensor_l2norm_scale,
+          "Computes L2 norm for a list of contiguous tensors and does scaling");
+    m.def("multi_tensor_lamb_stage1_cuda", &multi_tensor_lamb_stage1_cuda, "Computes update part of LAMB optimizer");
+    m.def("multi_tensor_lamb_stage2_cuda", &multi_tensor_lamb_stage2_cuda,
+          "Completes application of gradient to parameters for LAMB optimizer");
+    m.def("multi_tensor_adam", &multi_tensor_adam, "Compute and apply gradient update to parameters for Adam optimizer");
+    m.def("multi_tensor_lamb", &multi_tensor_lamb, "Computes and apply update for LAMB optimizer");
+    m.def("multi_tensor_fused_adam", &multi_tensor_fused_adam, "Mixed-precision / sharded Adam (DistAdamFunctor)",
+          py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor_beta1"),
+          py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),
+          py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
+          py::arg("honour_noop") = false);
+    m.def("launch_count", []() { return mt_launch_count(); }, "kernels launched by libmt_b200.so since load");
+    m.def("table_cache_stats", &table_cache_stats, "device tensor-table cache counters");
+    m.def("table_cache_clear", [](int device) { check(mt_table_cache_clear(device)); });
+    m.def("version", []() { return std::string(mt_version()); });
+}

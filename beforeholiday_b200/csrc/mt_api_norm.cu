@@ -1,0 +1,121 @@
+// mt_api_norm.cu -- multi_tensor_l2norm / multi_tensor_l2norm_scale entry points and the norm finalize kernel.
+//
+// Pass 1 (persistent grid, one tile == one reference chunk): per-tile sum of squares -> scratch partials[tile],
+// flag raised when a tile's partial is non-finite (the reference's per-chunk definition,
+// /root/reference/csrc/multi_tensor_l2norm_kernel.cu:103-104).
+// Pass 2 (norm_finalize_kernel): fixed-order reduction of the partials -> global norm and per-tensor norms.
+// Deterministic (no float atomics); replaces cleanup / cleanup_v3 (csrc/multi_tensor_l2norm_kernel.cu:198-237).
+#include "mt_host.h"
+#include "mt_ops.cuh"
+
+namespace mt {
+
+constexpr int kFinThreads = 512;
+
+// partials: [nsets][ntiles].  ret_global[s] (may be NULL) = sqrt(sum over all tiles of set s), by block 0.
+// ret_pt + s*ntensors (may be NULL) = per-tensor norms of set s: one warp per tensor, lanes stride the tensor's
+// tiles, fixed shuffle tree.
+__global__ void __launch_bounds__(kFinThreads)
+norm_finalize_kernel(const float* __restrict__ partials, int nsets, uint32_t ntiles,
+                     const uint32_t* __restrict__ tile_begin, int ntensors, float* __restrict__ ret_global,
+                     float* __restrict__ ret_pt) {
+    __shared__ float smem[kFinThreads / 32];
+    if (blockIdx.x == 0 && ret_global) {
+        for (int s = 0; s < nsets; s++) {
+            float acc = 0.f;
+            for (uint32_t i = threadIdx.x; i < ntiles; i += kFinThreads) acc = fadd(acc, partials[(size_t)s * ntiles + i]);
+            const float tot = block_sum<kFinThreads>(acc, smem);
+            if (threadIdx.x == 0) ret_global[s] = fsqrt(tot);
+        }
+    }
+    if (ret_pt) {
+        const int lane = threadIdx.x & 31;
+        const int warps = (gridDim.x * kFinThreads) >> 5;
+        for (int w = (blockIdx.x * kFinThreads + threadIdx.x) >> 5; w < ntensors * nsets; w += warps) {
+            const int s = w / ntensors, t = w - s * ntensors;
+            const uint32_t b = tile_begin[t], e = tile_begin[t + 1];
+            float acc = 0.f;
+            for (uint32_t i = b + lane; i < e; i += 32) acc = fadd(acc, partials[(size_t)s * ntiles + i]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc = fadd(acc, __shfl_xor_sync(0xffffffffu, acc, o));
+            if (lane == 0) ret_pt[(size_t)s * ntensors + t] = fsqrt(acc);
+        }
+    }
+}
+
+int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
+                         int device, cudaStream_t stream) {
+    DeviceInfo di;
+    int rc = device_info(device, &di);
+    if (rc) return rc;
+    int grid = 1;
+    if (ret_pt) {
+        const long long warps_needed = (long long)tb.ntensors * nsets;
+        long long blocks = (warps_needed + (kFinThreads / 32) - 1) / (kFinThreads / 32);
+        const long long cap = (long long)di.sms * 4;
+        grid = (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+    }
+    norm_finalize_kernel<<<grid, kFinThreads, 0, stream>>>(partials, nsets, tb.ntiles, tb.tile_begin, tb.ntensors,
+                                                           ret_global, ret_pt);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    MT_CUDA_OK(cudaGetLastError());
+    return MT_OK;
+}
+
+static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int depth,
+                       float scale, int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
+                       size_t scratch_bytes, cudaStream_t stream) {
+    int rc = validate_lists(tl, depth, depth, who);
+    if (rc) return rc;
+    if (chunk_size <= 0) return set_error(MT_EINVAL, "%s: chunk_size must be positive", who);
+    if (!noop_flag || !ret) return set_error(MT_EINVAL, "%s: noop_flag / ret is NULL", who);
+    if (per_tensor && !ret_per_tensor) return set_error(MT_EINVAL, "%s: per_tensor requested but ret_per_tensor is NULL", who);
+    DeviceGuard guard(tl->device);
+    if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
+    DevTable tb;
+    rc = get_table(tl, chunk_size, stream, &tb);
+    if (rc) return rc;
+    const size_t need = (size_t)tb.ntiles * sizeof(float);
+    if (need > 0 && (!scratch || scratch_bytes < need))
+        return set_error(MT_ESCRATCH, "%s: scratch too small (%zu < %zu bytes)", who, scratch_bytes, need);
+    float* partials = static_cast<float*>(scratch);
+    // 2 groups in flight per thread: a pure reduction has registers to spare
+    constexpr int G = 8, U = 2, THREADS = 512, MINB = 2;
+    if (depth == 1) {
+        MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
+            using Op = L2NormOp<Tx>;
+            typename Op::Params prm{partials};
+            rc = launch_persistent<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+        })
+    } else {
+        MT_DISPATCH_FHB(tl->dtype[0], Tin, who,
+            MT_DISPATCH_FHB(tl->dtype[1], Tout, who, {
+                using Op = L2NormScaleOp<Tin, Tout>;
+                typename Op::Params prm{partials, scale};
+                rc = launch_persistent<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+            }))
+    }
+    if (rc) return rc;
+    return launch_norm_finalize(tb, partials, 1, ret, per_tensor ? ret_per_tensor : nullptr, tl->device, stream);
+}
+
+}  // namespace mt
+
+extern "C" size_t mt_norm_scratch_bytes(int chunk_size, const MtTensorLists* tl) {
+    if (!tl || !tl->numel || chunk_size <= 0) return 0;
+    return (size_t)mt::count_tiles(tl, chunk_size) * sizeof(float);
+}
+
+extern "C" int mt_multi_tensor_l2norm(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
+                                      float* ret, float* ret_per_tensor, void* scratch, size_t scratch_bytes,
+                                      void* stream) {
+    return mt::norm_common("multi_tensor_l2norm", chunk_size, noop_flag, tl, 1, 0.f, per_tensor, ret, ret_per_tensor,
+                           scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mt_multi_tensor_l2norm_scale(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float scale,
+                                            int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
+                                            size_t scratch_bytes, void* stream) {
+    return mt::norm_common("multi_tensor_l2norm_scale", chunk_size, noop_flag, tl, 2, scale, per_tensor, ret,
+                           ret_per_tensor, scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
+}

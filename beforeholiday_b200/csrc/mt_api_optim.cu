@@ -1,0 +1,240 @@
+// mt_api_optim.cu -- optimizer entry points: Adam, mixed-precision (sharded) Adam, SGD, LAMB, legacy split LAMB.
+#include <cmath>
+
+#include "mt_host.h"
+#include "mt_ops.cuh"
+
+namespace mt {
+
+constexpr int kG = 8, kU = 1, kThreads = 512, kMinBlocks = 2;
+
+int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
+                         int device, cudaStream_t stream);  // mt_api_norm.cu
+
+// Host-side bias corrections: /root/reference/csrc/multi_tensor_adam.cu:145-149.  std::pow(float, int)
+// promotes to double; the result is rounded to float.
+static void bias_corrections(float beta1, float beta2, int step, int bias_correction, float* bc1, float* bc2) {
+    *bc1 = 1.0f;
+    *bc2 = 1.0f;
+    if (bias_correction == 1) {
+        *bc1 = (float)(1.0 - std::pow((double)beta1, (double)step));
+        *bc2 = (float)(1.0 - std::pow((double)beta2, (double)step));
+    }
+}
+
+static inline size_t align256(size_t x) { return (x + 255) / 256 * 256; }
+
+struct LambScratch {
+    size_t off_partials, off_pnorm, off_unorm, total;
+};
+static LambScratch lamb_scratch_layout(uint64_t ntiles, int64_t ntensors) {
+    LambScratch s;
+    s.off_partials = 0;
+    s.off_pnorm = align256(2 * (size_t)ntiles * sizeof(float));
+    s.off_unorm = s.off_pnorm + (size_t)ntensors * sizeof(float);  // contiguous with pnorm: finalize writes [2][ntensors]
+    s.total = align256(s.off_unorm + (size_t)ntensors * sizeof(float));
+    return s;
+}
+
+}  // namespace mt
+
+#define MT_PROLOGUE(who, lo, hi)                                                                    \
+    using namespace mt;                                                                             \
+    (void)chunk_size;                                                                               \
+    int rc = validate_lists(tl, lo, hi, who);                                                       \
+    if (rc) return rc;                                                                              \
+    if (!noop_flag) return set_error(MT_EINVAL, who ": noop_flag is NULL");                         \
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);                                       \
+    DeviceGuard guard(tl->device);                                                                  \
+    if (!guard.ok) return set_error(MT_ECUDA, who ": cannot select CUDA device %d", tl->device);
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float lr, float beta1,
+                                    float beta2, float epsilon, int step, int mode, int bias_correction,
+                                    float weight_decay, void* stream_) {
+    MT_PROLOGUE("multi_tensor_adam", 4, 4)
+    for (int d = 1; d < 4; d++)
+        if (tl->dtype[d] != tl->dtype[0])
+            return set_error(MT_EINVAL, "multi_tensor_adam: g, p, m, v must share one dtype (as the reference assumes)");
+    float bc1, bc2;
+    bias_corrections(beta1, beta2, step, bias_correction, &bc1, &bc2);
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+#define MT_ADAM(CT)                                                                                       \
+    {                                                                                                     \
+        using Op = AdamOp<CT>;                                                                            \
+        typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay, mode};                 \
+        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+    }
+    switch (tl->dtype[0]) {
+        case MT_F32: MT_ADAM(float)
+        case MT_F16: MT_ADAM(__half)
+        case MT_BF16: MT_ADAM(__nv_bfloat16)
+        case MT_F64: MT_ADAM(double)
+        default: return set_error(MT_EINVAL, "multi_tensor_adam: unsupported dtype tag %d", tl->dtype[0]);
+    }
+#undef MT_ADAM
+}
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                          const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                          const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                                          int mode, int honour_noop, void* stream_) {
+    MT_PROLOGUE("multi_tensor_fused_adam", 4, 5)
+    if (!per_tensor_beta1 || !per_tensor_beta2 || !per_tensor_bias_correction || !per_tensor_eps || !per_tensor_weight_decay)
+        return set_error(MT_EINVAL, "multi_tensor_fused_adam: per-tensor hyper-parameter arrays must be device pointers");
+    for (int d = 0; d < 3; d++)
+        if (tl->dtype[d] != MT_F32)
+            return set_error(MT_EINVAL, "multi_tensor_fused_adam: p, m, v must be float32");
+    if (tl->depth == 5 && tl->dtype[4] != tl->dtype[3])
+        return set_error(MT_EINVAL, "multi_tensor_fused_adam: p_copy must have the gradient dtype");
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    const bool copy = tl->depth == 5;
+#define MT_DADAM(TG, COPY, HN)                                                                            \
+    {                                                                                                     \
+        using Op = DistAdamOp<TG, COPY, HN>;                                                              \
+        typename Op::Params prm{per_tensor_beta1, per_tensor_beta2, per_tensor_eps, per_tensor_weight_decay, \
+                                per_tensor_bias_correction, lr, grad_scale, step, mode};                  \
+        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+    }
+    MT_DISPATCH_FHB(tl->dtype[3], Tg, "multi_tensor_fused_adam", {
+        if (copy) { if (honour_noop) MT_DADAM(Tg, true, true) else MT_DADAM(Tg, true, false) }
+        else      { if (honour_noop) MT_DADAM(Tg, false, true) else MT_DADAM(Tg, false, false) }
+    })
+#undef MT_DADAM
+    return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mt_multi_tensor_sgd(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float wd,
+                                   float momentum, float dampening, float lr, int nesterov, int first_run,
+                                   int wd_after_momentum, float scale, void* stream_) {
+    MT_PROLOGUE("multi_tensor_sgd", 3, 4)
+    const int gt = tl->dtype[0], wt = tl->dtype[1];
+    if (tl->dtype[2] != wt) return set_error(MT_EINVAL, "multi_tensor_sgd: momentum dtype must equal the weight dtype");
+    if (tl->depth == 4 && tl->dtype[3] != MT_F16)
+        return set_error(MT_EINVAL, "Additional output tensors should always be fp16.");
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+#define MT_SGD(TG, TW, COPY)                                                                              \
+    {                                                                                                     \
+        using Op = SgdOp<TG, TW, COPY>;                                                                   \
+        typename Op::Params prm{wd, momentum, dampening, lr, scale, nesterov, first_run, wd_after_momentum}; \
+        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+    }
+    // the reference's six combinations, /root/reference/csrc/multi_tensor_sgd_kernel.cu:165-314
+    if (gt == MT_F16 && wt == MT_F16 && tl->depth == 3) MT_SGD(__half, __half, false)
+    if (gt == MT_F32 && wt == MT_F32 && tl->depth == 3) MT_SGD(float, float, false)
+    if (gt == MT_F16 && wt == MT_F32 && tl->depth == 4) MT_SGD(__half, float, true)
+    if (gt == MT_F32 && wt == MT_F32 && tl->depth == 4) MT_SGD(float, float, true)
+    if (gt == MT_BF16 && wt == MT_BF16 && tl->depth == 3) MT_SGD(__nv_bfloat16, __nv_bfloat16, false)
+    if (gt == MT_BF16 && wt == MT_F32 && tl->depth == 4) MT_SGD(__nv_bfloat16, float, true)
+#undef MT_SGD
+    return set_error(MT_EINVAL,
+                     "multi_tensor_sgd only supports some combinations of gradient & weight types. Given: "
+                     "gradient: %d, weight: %d, num_lists: %d", gt, wt, tl->depth);
+}
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" size_t mt_lamb_scratch_bytes(int chunk_size, const MtTensorLists* tl) {
+    (void)chunk_size;
+    if (!tl || !tl->numel || tl->ntensors <= 0) return 0;
+    const int tile = mt::choose_tile_elems(tl, tl->device);
+    return mt::lamb_scratch_layout(mt::count_tiles(tl, tile), tl->ntensors).total;
+}
+
+extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float lr, float beta1,
+                                    float beta2, float epsilon, int step, int bias_correction, float weight_decay,
+                                    int grad_averaging, int mode, const float* global_grad_norm, float max_grad_norm,
+                                    int use_nvlamb, void* scratch, size_t scratch_bytes, void* stream_) {
+    MT_PROLOGUE("multi_tensor_lamb", 4, 4)
+    if (!global_grad_norm) return set_error(MT_EINVAL, "multi_tensor_lamb: global_grad_norm must be a device pointer");
+    for (int d = 1; d < 4; d++)
+        if (tl->dtype[d] != tl->dtype[0])
+            return set_error(MT_EINVAL, "multi_tensor_lamb: g, p, m, v must share one dtype (as the reference assumes)");
+    float bc1, bc2;
+    bias_corrections(beta1, beta2, step, bias_correction, &bc1, &bc2);
+    float beta3 = 1.0f;
+    if (grad_averaging == 1) beta3 = 1 - beta1;  // csrc/multi_tensor_lamb.cu:363-364
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    const LambScratch lay = lamb_scratch_layout(tb.ntiles, tl->ntensors);
+    if (!scratch || scratch_bytes < lay.total)
+        return set_error(MT_ESCRATCH, "multi_tensor_lamb: scratch too small (%zu < %zu bytes)", scratch_bytes, lay.total);
+    char* sc = static_cast<char*>(scratch);
+    float* partials = reinterpret_cast<float*>(sc + lay.off_partials);
+    float* pnorm = reinterpret_cast<float*>(sc + lay.off_pnorm);
+    float* unorm = reinterpret_cast<float*>(sc + lay.off_unorm);
+    // The per-tensor norms only feed the trust ratio, which stage 2 ignores unless use_nvlamb || decay != 0
+    // (csrc/multi_tensor_lamb.cu:255-263): skip both norm passes otherwise.
+    const int need_norms = (use_nvlamb || weight_decay != 0.0f) ? 1 : 0;
+
+    MT_DISPATCH_FHB(tl->dtype[0], Tp, "multi_tensor_lamb", {
+        using Op1 = LambStage1Op<Tp>;
+        typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
+                                global_grad_norm, partials, tb.ntiles, mode, need_norms};
+        rc = launch_persistent<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+        if (rc) return rc;
+        if (need_norms) {
+            rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream);
+            if (rc) return rc;
+        }
+        // stage 2 walks lists [u (= g), p] of the SAME table: list indices 0 and 1
+        using Op2 = LambStage2Op<Tp>;
+        typename Op2::Params p2{pnorm, unorm, lr, weight_decay, use_nvlamb};
+        return launch_persistent<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);
+    })
+    return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mt_multi_tensor_lamb_stage1(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                           const float* per_tensor_decay, int step, float beta1, float beta2,
+                                           float epsilon, float global_grad_norm, float max_global_grad_norm,
+                                           void* stream_) {
+    MT_PROLOGUE("multi_tensor_lamb_stage1_cuda", 5, 5)
+    if (!per_tensor_decay) return set_error(MT_EINVAL, "multi_tensor_lamb_stage1_cuda: per_tensor_decay is NULL");
+    if (tl->dtype[2] != tl->dtype[1] || tl->dtype[3] != tl->dtype[1])
+        return set_error(MT_EINVAL, "multi_tensor_lamb_stage1_cuda: p, m, v must share one dtype");
+    // csrc/multi_tensor_lamb_stage_1.cu:126-130
+    const float clip = global_grad_norm > max_global_grad_norm ? global_grad_norm / max_global_grad_norm : 1.0f;
+    const float next_step = (float)(step + 1);
+    const float bc1 = 1.0f - std::pow(beta1, next_step);
+    const float bc2 = 1.0f - std::pow(beta2, next_step);
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    MT_DISPATCH_FHB(tl->dtype[0], Tg, "lamb_stage_1",
+        MT_DISPATCH_FHB(tl->dtype[1], Tp, "lamb_stage_1",
+            MT_DISPATCH_FHB(tl->dtype[4], Tu, "lamb_stage_1", {
+                using Op = LambStage1LegacyOp<Tg, Tp, Tu>;
+                typename Op::Params prm{per_tensor_decay, beta1, beta2, bc1, bc2, epsilon, clip};
+                return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+            })))
+    return MT_OK;
+}
+
+extern "C" int mt_multi_tensor_lamb_stage2(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                           const float* per_tensor_param_norm, const float* per_tensor_update_norm,
+                                           float lr, float weight_decay, int use_nvlamb, void* stream_) {
+    MT_PROLOGUE("multi_tensor_lamb_stage2_cuda", 2, 2)
+    if (!per_tensor_param_norm || !per_tensor_update_norm)
+        return set_error(MT_EINVAL, "multi_tensor_lamb_stage2_cuda: norm arrays are NULL");
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    MT_DISPATCH_FHB(tl->dtype[0], Tp, "lamb_stage_2",
+        MT_DISPATCH_FHB(tl->dtype[1], Tu, "lamb_stage_2", {
+            using Op = LambStage2LegacyOp<Tp, Tu>;
+            typename Op::Params prm{per_tensor_param_norm, per_tensor_update_norm, lr, weight_decay, use_nvlamb};
+            return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+        }))
+    return MT_OK;
+}

@@ -1,0 +1,431 @@
+// mt_common.cuh -- device-side machinery shared by every multi-tensor kernel.
+//
+// Replaces the reference's chunk launcher (/root/reference/csrc/multi_tensor_apply.cuh:16-147): instead of
+// packing <=36..110 tensors / <=2560 chunks into a ~14 KB by-value kernel argument and launching repeatedly,
+// one persistent grid walks a DEVICE-RESIDENT tensor table:
+//
+//   DevTable { ptrs[depth][ntensors], numel[ntensors], tile_begin[ntensors+1] }   (built + cached by mt_table.cu)
+//
+// Work unit = "tile": `tile_elems` consecutive elements of one tensor.  CTA b processes tiles b, b+grid, ...
+// The owning tensor is found with a binary search in tile_begin (uniform across the CTA -> broadcast loads).
+// Inside a tile each thread moves G consecutive elements per access: 32 B (LDG.256/STG.256) for fp32 and 16 B
+// for 16-bit types at G = 8, fully coalesced; a per-tile scalar head/tail peel handles arbitrary element
+// offsets (shard fragments, odd sizes) without dropping the whole tile to scalar code the way the reference's
+// is_aligned() test does (csrc/multi_tensor_scale_kernel.cu:59).
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace mt {
+
+struct DevTable {
+    const void* const* ptrs;     // [depth][ntensors], list-major
+    const int64_t* numel;        // [ntensors]
+    const uint32_t* tile_begin;  // [ntensors + 1] exclusive prefix sum of per-tensor tile counts
+    int32_t ntensors;
+    uint32_t ntiles;
+    int32_t tile_elems;
+};
+
+// ------------------------------------------------------------------------------------------------
+// IEEE-754 binary32 arithmetic that the compiler may not contract into FMA.  The CPU oracle
+// (oracle/mt_oracle.c) performs the same operations in the same order, so fp32 results are bit-identical.
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ float fsqrt(float a) { return __fsqrt_rn(a); }
+__device__ __forceinline__ bool finite_f(float a) { return (__float_as_uint(a) & 0x7f800000u) != 0x7f800000u; }
+
+// ------------------------------------------------------------------------------------------------
+// Element types.
+template <class T> struct Elem;
+template <> struct Elem<float> {
+    static constexpr int kBytes = 4;
+    __device__ static __forceinline__ float load(const float* p) { return *p; }
+    __device__ static __forceinline__ void store(float* p, float v) { *p = v; }
+    __device__ static __forceinline__ float round(float v) { return v; }
+};
+template <> struct Elem<double> {
+    static constexpr int kBytes = 8;
+    __device__ static __forceinline__ float load(const double* p) { return (float)*p; }
+    __device__ static __forceinline__ void store(double* p, float v) { *p = (double)v; }
+    __device__ static __forceinline__ float round(float v) { return v; }
+};
+template <> struct Elem<__half> {
+    static constexpr int kBytes = 2;
+    __device__ static __forceinline__ float load(const __half* p) { return __half2float(*p); }
+    __device__ static __forceinline__ void store(__half* p, float v) { *p = __float2half_rn(v); }
+    __device__ static __forceinline__ float round(float v) { return __half2float(__float2half_rn(v)); }
+};
+template <> struct Elem<__nv_bfloat16> {
+    static constexpr int kBytes = 2;
+    __device__ static __forceinline__ float load(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+    __device__ static __forceinline__ void store(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+    __device__ static __forceinline__ float round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Raw vector accesses (N 32-bit words).  Streaming data is touched exactly once per step, so nothing is
+// allocated in L1 (L1::no_allocate).  The non-coherent (.nc) path is deliberately NOT used even for input-only
+// lists: in-place calls, where an output list aliases an input list, are legal for this API
+// (/root/reference/tests/L0/run_amp/test_multi_tensor_scale.py:58-77).
+template <int N, bool RO> struct RawVec;
+
+template <bool RO> struct RawVec<2, RO> {
+    __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[2]) {
+        asm volatile("ld.global.L1::no_allocate.v2.b32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p) : "memory");
+    }
+    __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[2]) {
+        asm volatile("st.global.L1::no_allocate.v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(w[0]), "r"(w[1]) : "memory");
+    }
+};
+template <bool RO> struct RawVec<4, RO> {
+    __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[4]) {
+        asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
+    }
+    __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[4]) {
+        asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w[0]), "r"(w[1]),
+                     "r"(w[2]), "r"(w[3]) : "memory");
+    }
+};
+// 256-bit global accesses are an sm_100 addition (SASS: LDG.E.256 / STG.E.256).
+template <bool RO> struct RawVec<8, RO> {
+    __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[8]) {
+        asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                         : "l"(p) : "memory");
+    }
+    __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[8]) {
+        asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]),
+                     "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
+    }
+};
+
+// Typed group access: G consecutive elements <-> float[G].
+template <class T, int G, bool RO> struct Group;
+
+template <int G, bool RO> struct Group<float, G, RO> {
+    __device__ static __forceinline__ void ld(const float* p, float (&f)[G]) {
+        uint32_t w[G];
+        RawVec<G, RO>::ld(p, w);
+#pragma unroll
+        for (int i = 0; i < G; i++) f[i] = __uint_as_float(w[i]);
+    }
+    __device__ static __forceinline__ void st(float* p, const float (&f)[G]) {
+        uint32_t w[G];
+#pragma unroll
+        for (int i = 0; i < G; i++) w[i] = __float_as_uint(f[i]);
+        RawVec<G, RO>::st(p, w);
+    }
+};
+template <int G, bool RO> struct Group<__half, G, RO> {
+    __device__ static __forceinline__ void ld(const __half* p, float (&f)[G]) {
+        uint32_t w[G / 2];
+        RawVec<G / 2, RO>::ld(p, w);
+#pragma unroll
+        for (int i = 0; i < G / 2; i++) {
+            float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+            f[2 * i] = t.x;
+            f[2 * i + 1] = t.y;
+        }
+    }
+    __device__ static __forceinline__ void st(__half* p, const float (&f)[G]) {
+        uint32_t w[G / 2];
+#pragma unroll
+        for (int i = 0; i < G / 2; i++) {
+            __half2 h = __floats2half2_rn(f[2 * i], f[2 * i + 1]);
+            w[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        RawVec<G / 2, RO>::st(p, w);
+    }
+};
+template <int G, bool RO> struct Group<__nv_bfloat16, G, RO> {
+    __device__ static __forceinline__ void ld(const __nv_bfloat16* p, float (&f)[G]) {
+        uint32_t w[G / 2];
+        RawVec<G / 2, RO>::ld(p, w);
+#pragma unroll
+        for (int i = 0; i < G / 2; i++) {  // bf16 -> f32 is a 16-bit shift
+            f[2 * i] = __uint_as_float(w[i] << 16);
+            f[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+        }
+    }
+    __device__ static __forceinline__ void st(__nv_bfloat16* p, const float (&f)[G]) {
+        uint32_t w[G / 2];
+#pragma unroll
+        for (int i = 0; i < G / 2; i++) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+            w[i] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        RawVec<G / 2, RO>::st(p, w);
+    }
+};
+template <int G, bool RO> struct Group<double, G, RO> {  // rare (Adam dispatches on double); 32-B pieces
+    __device__ static __forceinline__ void ld(const double* p, float (&f)[G]) {
+#pragma unroll
+        for (int k = 0; k < G / 4; k++) {
+            uint32_t w[8];
+            RawVec<8, RO>::ld(p + 4 * k, w);
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                f[4 * k + i] = (float)__hiloint2double((int)w[2 * i + 1], (int)w[2 * i]);
+        }
+    }
+    __device__ static __forceinline__ void st(double* p, const float (&f)[G]) {
+#pragma unroll
+        for (int k = 0; k < G / 4; k++) {
+            uint32_t w[8];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                double d = (double)f[4 * k + i];
+                w[2 * i] = (uint32_t)__double2loint(d);
+                w[2 * i + 1] = (uint32_t)__double2hiint(d);
+            }
+            RawVec<8, RO>::st(p + 4 * k, w);
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Tile lookup.
+struct Tile {
+    int32_t tensor;
+    int32_t len;    // elements in this tile (<= tile_elems)
+    int64_t start;  // element offset inside the tensor
+};
+
+__device__ __forceinline__ Tile locate_tile(const DevTable& tb, uint32_t tile) {
+    // upper_bound(tile_begin, tile) - 1 : last tensor whose first tile is <= tile.  Empty tensors have
+    // tile_begin[t] == tile_begin[t+1] and are skipped naturally.
+    int lo = 0, hi = tb.ntensors;  // invariant: tile_begin[lo] <= tile < tile_begin[hi]
+    while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (__ldg(tb.tile_begin + mid) <= tile) lo = mid; else hi = mid;
+    }
+    Tile t;
+    t.tensor = lo;
+    uint32_t k = tile - __ldg(tb.tile_begin + lo);
+    t.start = (int64_t)k * tb.tile_elems;
+    int64_t rem = __ldg(tb.numel + lo) - t.start;
+    t.len = rem < tb.tile_elems ? (int32_t)rem : tb.tile_elems;
+    return t;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Block reductions (deterministic: fixed shuffle tree, fixed warp order).
+template <int THREADS> __device__ __forceinline__ float block_sum(float v, float* smem /* >= THREADS/32 floats */) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fadd(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();  // protect smem reuse across calls
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (warp == 0) {
+        r = lane < THREADS / 32 ? smem[lane] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r = fadd(r, __shfl_xor_sync(0xffffffffu, r, o));
+    }
+    return r;  // valid in warp 0 (all lanes)
+}
+
+// ------------------------------------------------------------------------------------------------
+// Op concept (all static / const, so everything inlines):
+//
+//   static constexpr int kLists;                 number of tensor lists
+//   template <int D> using T = ...;              element type of list D
+//   static constexpr unsigned kRead, kWrite;     bit d set: list d is loaded / stored
+//   static constexpr bool kEarlyExit;            return at once if *noop != 0
+//   struct Params;                               POD kernel argument
+//   struct State;                                per-thread running state (flags, partial sums)
+//   __device__ void begin_tensor(int t);         per-tile, uniform: fetch per-tensor scalars
+//   __device__ bool load(int d) / store(int d);  runtime (uniform) refinement of kRead / kWrite
+//   __device__ void elem(float (&x)[kLists], State&);   one element: inputs in x, outputs written to x
+//   template <int THREADS> __device__ void end_tile_n(uint32_t tile, State&, float* smem, int32_t* noop);
+//                                                (norm ops: block reduce + per-tile partial + flag)
+//   __device__ void finish(State&, int32_t* noop);                  (flag ops)
+//
+template <class Op, int D> using ListT = typename Op::template T<D>;
+
+template <class Op, int G, int D, bool kVec>
+__device__ __forceinline__ void load_list(const Op& op, char* const (&base)[Op::kLists], int64_t idx,
+                                          float (&x)[Op::kLists][G]) {
+    using T = ListT<Op, D>;
+    if constexpr (((Op::kRead >> D) & 1u) != 0) {
+        if (op.load(D)) {
+            const T* p = reinterpret_cast<const T*>(base[D]) + idx;
+            constexpr bool RO = ((Op::kWrite >> D) & 1u) == 0;
+            if constexpr (kVec) Group<T, G, RO>::ld(p, x[D]);
+            else x[D][0] = Elem<T>::load(p);
+            return;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < G; i++) x[D][i] = 0.f;
+}
+
+template <class Op, int G, int D, bool kVec>
+__device__ __forceinline__ void store_list(const Op& op, char* const (&base)[Op::kLists], int64_t idx,
+                                           const float (&x)[Op::kLists][G]) {
+    using T = ListT<Op, D>;
+    if constexpr (((Op::kWrite >> D) & 1u) != 0) {
+        if (op.store(D)) {
+            T* p = reinterpret_cast<T*>(base[D]) + idx;
+            if constexpr (kVec) Group<T, G, false>::st(p, x[D]);
+            else Elem<T>::store(p, x[D][0]);
+        }
+    }
+}
+
+template <class Op, int G, bool kVec, int... Ds>
+__device__ __forceinline__ void load_all(const Op& op, char* const (&base)[Op::kLists], int64_t idx,
+                                         float (&x)[Op::kLists][G], std::integer_sequence<int, Ds...>) {
+    (load_list<Op, G, Ds, kVec>(op, base, idx, x), ...);
+}
+template <class Op, int G, bool kVec, int... Ds>
+__device__ __forceinline__ void store_all(const Op& op, char* const (&base)[Op::kLists], int64_t idx,
+                                          const float (&x)[Op::kLists][G], std::integer_sequence<int, Ds...>) {
+    (store_list<Op, G, Ds, kVec>(op, base, idx, x), ...);
+}
+
+template <class Op, int G>
+__device__ __forceinline__ void compute_group(const Op& op, float (&x)[Op::kLists][G], typename Op::State& st) {
+#pragma unroll
+    for (int i = 0; i < G; i++) {
+        float e[Op::kLists];
+#pragma unroll
+        for (int d = 0; d < Op::kLists; d++) e[d] = x[d][i];
+        op.elem(e, st);
+#pragma unroll
+        for (int d = 0; d < Op::kLists; d++) x[d][i] = e[d];
+    }
+}
+
+// One scalar element (head / tail peel and the mutually-misaligned fallback).
+template <class Op>
+__device__ __forceinline__ void scalar_elem(const Op& op, char* const (&base)[Op::kLists], int64_t idx,
+                                            typename Op::State& st) {
+    using Seq = std::make_integer_sequence<int, Op::kLists>;
+    float x[Op::kLists][1];
+    load_all<Op, 1, false>(op, base, idx, x, Seq{});
+    compute_group<Op, 1>(op, x, st);
+    store_all<Op, 1, false>(op, base, idx, x, Seq{});
+}
+
+// Common head: number of leading elements h in [0, G) after which EVERY list is aligned to its G-element
+// vector (G * sizeof(T) bytes).  -1 if the lists are mutually misaligned (no such h).
+template <class Op, int G, int... Ds>
+__device__ __forceinline__ int common_head(char* const (&base)[Op::kLists], int64_t start,
+                                           std::integer_sequence<int, Ds...>) {
+    int mis[Op::kLists] = {
+        (int)(((reinterpret_cast<uintptr_t>(base[Ds]) / sizeof(ListT<Op, Ds>)) + (uint64_t)start) % G)...};
+    bool same = true;
+#pragma unroll
+    for (int d = 1; d < Op::kLists; d++) same = same && (mis[d] == mis[0]);
+    return same ? ((G - mis[0]) % G) : -1;
+}
+
+template <class Op, int G, int U, int THREADS>
+__device__ __forceinline__ void process_tile(const Op& op, char* const (&base)[Op::kLists], const Tile& t,
+                                             typename Op::State& st) {
+    using Seq = std::make_integer_sequence<int, Op::kLists>;
+    const int tid = threadIdx.x;
+    int h = common_head<Op, G>(base, t.start, Seq{});
+    if (h < 0) {  // mutually misaligned lists: coalesced element-wise path for this tile
+        for (int i = tid; i < t.len; i += THREADS) scalar_elem<Op>(op, base, t.start + i, st);
+        return;
+    }
+    if (h > t.len) h = t.len;
+    const int nvec = (t.len - h) / G;
+    const int64_t v0 = t.start + h;
+
+    for (int j0 = 0; j0 < nvec; j0 += THREADS * U) {
+        float x[U][Op::kLists][G];
+        if (j0 + THREADS * U <= nvec) {  // full round: all loads are issued before the first use
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                load_all<Op, G, true>(op, base, v0 + (int64_t)(j0 + u * THREADS + tid) * G, x[u], Seq{});
+#pragma unroll
+            for (int u = 0; u < U; u++) compute_group<Op, G>(op, x[u], st);
+#pragma unroll
+            for (int u = 0; u < U; u++)
+                store_all<Op, G, true>(op, base, v0 + (int64_t)(j0 + u * THREADS + tid) * G, x[u], Seq{});
+        } else {
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int j = j0 + u * THREADS + tid;
+                if (j < nvec) load_all<Op, G, true>(op, base, v0 + (int64_t)j * G, x[u], Seq{});
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int j = j0 + u * THREADS + tid;
+                if (j < nvec) {
+                    compute_group<Op, G>(op, x[u], st);
+                    store_all<Op, G, true>(op, base, v0 + (int64_t)j * G, x[u], Seq{});
+                }
+            }
+        }
+    }
+    // scalar edges: [0, h) and [h + nvec*G, len): at most 2*(G-1) elements
+    const int tail0 = h + nvec * G;
+    const int nedge = h + (t.len - tail0);
+    if (tid < nedge) scalar_elem<Op>(op, base, t.start + (tid < h ? tid : tail0 + (tid - h)), st);
+}
+
+template <class Op, int... Ds>
+__device__ __forceinline__ void fetch_bases(const DevTable& tb, int tensor, char* (&base)[Op::kLists],
+                                            std::integer_sequence<int, Ds...>) {
+    ((base[Ds] = (char*)__ldg(reinterpret_cast<const unsigned long long*>(tb.ptrs) + (size_t)Ds * tb.ntensors + tensor)),
+     ...);
+}
+
+// The persistent kernel.  grid = min(ntiles, SMs * occupancy); static round-robin over tiles.
+template <class Op, int G, int U, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+mt_persistent_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __restrict__ noop) {
+    __shared__ float smem[THREADS / 32];
+    if (Op::kEarlyExit) {
+        if (*reinterpret_cast<volatile int32_t*>(noop) != 0) return;
+    }
+    Op op(prm);
+    typename Op::State st;
+    op.init(st);
+    using Seq = std::make_integer_sequence<int, Op::kLists>;
+    for (uint32_t tile = blockIdx.x; tile < tb.ntiles; tile += gridDim.x) {
+        const Tile t = locate_tile(tb, tile);
+        char* base[Op::kLists];
+        fetch_bases<Op>(tb, t.tensor, base, Seq{});
+        op.begin_tensor(t.tensor);
+        process_tile<Op, G, U, THREADS>(op, base, t, st);
+        op.template end_tile_n<THREADS>(tile, st, smem, noop);
+    }
+    op.finish(st, noop);
+}
+
+// Ops that neither keep per-tensor scalars nor reduce inherit these no-ops.
+struct OpBase {
+    struct State {};
+    static constexpr bool kEarlyExit = false;
+    __device__ __forceinline__ void init(State&) const {}
+    __device__ __forceinline__ void begin_tensor(int) {}
+    __device__ __forceinline__ bool load(int) const { return true; }
+    __device__ __forceinline__ bool store(int) const { return true; }
+    template <int THREADS, class S> __device__ __forceinline__ void end_tile_n(uint32_t, S&, float*, int32_t*) const {}
+    template <class S> __device__ __forceinline__ void finish(S&, int32_t*) const {}
+};
+
+// Flag state shared by scale / axpby: any thread that saw a non-finite input raises the flag once per CTA.
+struct FiniteState {
+    bool finite;
+};
+__device__ __forceinline__ void finish_finite(const FiniteState& st, int32_t* noop) {
+    if (__syncthreads_or(!st.finite)) {
+        if (threadIdx.x == 0) *noop = 1;
+    }
+}
+
+}  // namespace mt

@@ -1,0 +1,101 @@
+// mt_host.h -- host-side internals of libmt_b200.so shared by the per-family translation units:
+// error state, device guard, the device-resident table cache and the persistent-grid launcher.
+#pragma once
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <string>
+
+#include "../../include/mt_b200.h"
+#include "mt_common.cuh"
+
+namespace mt {
+
+// ---- error state (thread-local message, negative return codes) ---------------------------------
+int set_error(int code, const char* fmt, ...);
+#define MT_CUDA_OK(expr)                                                                          \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess)                                                                    \
+            return ::mt::set_error(MT_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+extern std::atomic<uint64_t> g_launches;
+
+struct DeviceGuard {
+    int prev = -1, cur = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        cur = dev;
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() {
+        if (ok && prev >= 0 && prev != cur) cudaSetDevice(prev);
+    }
+};
+
+struct DeviceInfo {
+    int sms = 0;
+};
+int device_info(int device, DeviceInfo* out);
+
+// ---- validation ---------------------------------------------------------------------------------
+// Mirrors the checks of /root/reference/csrc/multi_tensor_apply.cuh:53-72 that survive the loss of
+// torch types (depth, list lengths and numel equality are structural in MtTensorLists).
+int validate_lists(const MtTensorLists* tl, int expect_depth_lo, int expect_depth_hi, const char* who);
+int64_t total_elems(const MtTensorLists* tl);
+
+// ---- tiles ----------------------------------------------------------------------------------------
+// Element-wise ops ignore the caller's chunk_size and pick their own tile: 16384 elements when that still
+// yields enough tiles to balance a persistent grid, shrinking to 4096 for small problems.
+int choose_tile_elems(const MtTensorLists* tl, int device);
+uint64_t count_tiles(const MtTensorLists* tl, int tile_elems);
+
+// Look the (lists, tile_elems) pair up in the per-device table cache; on a miss build the table, upload it
+// (one cudaMemcpyAsync on `stream`) and cache it.  Steady-state steps with unchanged pointers upload nothing.
+int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevTable* out);
+
+// ---- launcher -------------------------------------------------------------------------------------
+template <class Op, int G, int U, int THREADS, int MINB>
+int launch_persistent(const DevTable& tb, const typename Op::Params& prm, int32_t* noop, int device,
+                      cudaStream_t stream) {
+    if (tb.ntiles == 0) return MT_OK;  // all tensors empty: nothing to do (the reference launches nothing either)
+    auto kernel = mt_persistent_kernel<Op, G, U, THREADS, MINB>;
+    // One occupancy query per (kernel instantiation, device): grid = resident CTAs per SM x SM count.
+    static std::atomic<int> limit_cache[64];
+    if (device < 0 || device >= 64) return set_error(MT_EINVAL, "device ordinal %d out of range", device);
+    int limit = limit_cache[device].load(std::memory_order_relaxed);
+    if (limit == 0) {
+        int occ = 0;
+        MT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, THREADS, 0));
+        DeviceInfo di;
+        int rc = device_info(device, &di);
+        if (rc) return rc;
+        limit = (occ > 0 ? occ : 1) * di.sms;
+        limit_cache[device].store(limit, std::memory_order_relaxed);
+    }
+    const unsigned grid = tb.ntiles < (uint32_t)limit ? tb.ntiles : (unsigned)limit;
+    kernel<<<grid, THREADS, 0, stream>>>(tb, prm, noop);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    MT_CUDA_OK(cudaGetLastError());
+    return MT_OK;
+}
+
+// dtype-tag dispatch helpers
+#define MT_CASE(TAG, CT, NAME, ...) \
+    case TAG: {                     \
+        using NAME = CT;            \
+        __VA_ARGS__;                \
+    } break;
+#define MT_DISPATCH_FHB(tag, NAME, who, ...)                                          \
+    switch (tag) {                                                                    \
+        MT_CASE(MT_F32, float, NAME, __VA_ARGS__)                                     \
+        MT_CASE(MT_F16, __half, NAME, __VA_ARGS__)                                    \
+        MT_CASE(MT_BF16, __nv_bfloat16, NAME, __VA_ARGS__)                            \
+        default:                                                                      \
+            return ::mt::set_error(MT_EINVAL, "%s: unsupported dtype tag %d", who, (int)(tag)); \
+    }
+
+}  // namespace mt

@@ -1,0 +1,337 @@
+// mt_ops.cuh -- the per-element functors (the "what"); mt_common.cuh is the "how".
+//
+// Each Op restates one reference functor in IEEE fp32, in the reference's operation order, with
+// non-contractable arithmetic (mt::fadd/fmul/...), so that it is bit-identical to oracle/mt_oracle.c.
+// Citations are file:line in /root/reference.
+#pragma once
+
+#include "mt_common.cuh"
+
+namespace mt {
+
+template <class A, class B = void, class C = void, class D = void, class E = void> struct Types {
+    template <int I> using at = std::conditional_t<I == 0, A, std::conditional_t<I == 1, B,
+                                std::conditional_t<I == 2, C, std::conditional_t<I == 3, D, E>>>>;
+};
+
+// ------------------------------------------------------------------------------------------------
+// ScaleFunctor: csrc/multi_tensor_scale_kernel.cu:68-69,108-109.   lists: in, out
+template <class Tin, class Tout> struct ScaleOp : OpBase {
+    static constexpr int kLists = 2;
+    template <int D> using T = typename Types<Tin, Tout>::template at<D>;
+    static constexpr unsigned kRead = 0b01, kWrite = 0b10;
+    struct Params { float scale; };
+    using State = FiniteState;
+    Params p;
+    __device__ explicit ScaleOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void init(State& s) const { s.finite = true; }
+    __device__ __forceinline__ void elem(float (&x)[2], State& s) const {
+        s.finite = s.finite && finite_f(x[0]);
+        x[1] = fmul(x[0], p.scale);
+    }
+    __device__ __forceinline__ void finish(State& s, int32_t* noop) const { finish_finite(s, noop); }
+};
+
+// AxpbyFunctor: csrc/multi_tensor_axpby_kernel.cu:73-79.   lists: x, y, out
+template <class Tx, class Ty, class To> struct AxpbyOp : OpBase {
+    static constexpr int kLists = 3;
+    template <int D> using T = typename Types<Tx, Ty, To>::template at<D>;
+    static constexpr unsigned kRead = 0b011, kWrite = 0b100;
+    struct Params { float a, b; int arg_to_check; };
+    using State = FiniteState;
+    Params p;
+    __device__ explicit AxpbyOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void init(State& s) const { s.finite = true; }
+    __device__ __forceinline__ void elem(float (&x)[3], State& s) const {
+        if (p.arg_to_check == -1) s.finite = s.finite && (finite_f(x[0]) && finite_f(x[1]));
+        if (p.arg_to_check == 0) s.finite = s.finite && finite_f(x[0]);
+        if (p.arg_to_check == 1) s.finite = s.finite && finite_f(x[1]);
+        x[2] = fadd(fmul(p.a, x[0]), fmul(p.b, x[1]));
+    }
+    __device__ __forceinline__ void finish(State& s, int32_t* noop) const { finish_finite(s, noop); }
+};
+
+// ------------------------------------------------------------------------------------------------
+// AdamFunctor: csrc/multi_tensor_adam.cu:94-112.   lists: g, p, m, v (one dtype, fp32 math)
+template <class Tp> struct AdamOp : OpBase {
+    static constexpr int kLists = 4;
+    template <int D> using T = Tp;
+    static constexpr unsigned kRead = 0b1111, kWrite = 0b1110;
+    struct Params { float beta1, beta2, bc1, bc2, eps, lr, decay; int mode; };
+    Params p;
+    float omb1, omb2;
+    __device__ explicit AdamOp(const Params& q) : p(q), omb1(fsub(1.f, q.beta1)), omb2(fsub(1.f, q.beta2)) {}
+    __device__ __forceinline__ void elem(float (&x)[4], State&) const {
+        float g = x[0], w = x[1], m = x[2], v = x[3];
+        if (p.mode == 0) {  // L2
+            g = fadd(g, fmul(p.decay, w));
+            m = fadd(fmul(p.beta1, m), fmul(omb1, g));
+            v = fadd(fmul(p.beta2, v), fmul(fmul(omb2, g), g));
+            const float denom = fadd(fsqrt(fdiv(v, p.bc2)), p.eps);
+            const float upd = fdiv(fdiv(m, p.bc1), denom);
+            w = fsub(w, fmul(p.lr, upd));
+        } else {  // AdamW
+            m = fadd(fmul(p.beta1, m), fmul(omb1, g));
+            v = fadd(fmul(p.beta2, v), fmul(fmul(omb2, g), g));
+            const float denom = fadd(fsqrt(fdiv(v, p.bc2)), p.eps);
+            const float upd = fadd(fdiv(fdiv(m, p.bc1), denom), fmul(p.decay, w));
+            w = fsub(w, fmul(p.lr, upd));
+        }
+        x[1] = w; x[2] = m; x[3] = v;
+    }
+};
+
+// DistAdamFunctor: apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:52-63,103-116.
+// lists: p, m, v (fp32), g (Tg) [, p_copy (Tg)].  Per-tensor hyper-parameters live in device arrays.
+template <class Tg, bool kCopy, bool kHonourNoop> struct DistAdamOp : OpBase {
+    static constexpr int kLists = kCopy ? 5 : 4;
+    template <int D> using T = typename Types<float, float, float, Tg, Tg>::template at<D>;
+    static constexpr unsigned kRead = 0b01111, kWrite = kCopy ? 0b10111 : 0b00111;
+    static constexpr bool kEarlyExit = kHonourNoop;
+    struct Params {
+        const float *beta1, *beta2, *eps, *decay;
+        const int32_t* bias_correction;
+        float lr, grad_scale;
+        int step, mode;
+    };
+    Params p;
+    float b1, b2, omb1, omb2, bc1, bc2, eps, decay;
+    int bc_on;
+    __device__ explicit DistAdamOp(const Params& q) : p(q), b1(-1.f), b2(-1.f), bc1(1.f), bc2(1.f), bc_on(-1) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        const float nb1 = __ldg(p.beta1 + t), nb2 = __ldg(p.beta2 + t);
+        const int on = __ldg(p.bias_correction + t) == 1;
+        eps = __ldg(p.eps + t); decay = __ldg(p.decay + t);
+        // The bias corrections cost two double pow(): recompute only when the hyper-parameters change between
+        // consecutive tiles of this CTA (they are almost always identical for every tensor).
+        if (nb1 != b1 || nb2 != b2 || on != bc_on) {
+            b1 = nb1; b2 = nb2; bc_on = on;
+            omb1 = fsub(1.f, b1); omb2 = fsub(1.f, b2);
+            bc1 = 1.f; bc2 = 1.f;
+            if (on) {
+                bc1 = (float)(1.0 - pow((double)b1, (double)p.step));
+                bc2 = (float)(1.0 - pow((double)b2, (double)p.step));
+            }
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[kLists], State&) const {
+        float w = x[0], m = x[1], v = x[2];
+        const float sg = fdiv(x[3], p.grad_scale);
+        m = fadd(fmul(b1, m), fmul(omb1, sg));
+        v = fadd(fmul(b2, v), fmul(fmul(omb2, sg), sg));
+        const float mu = fdiv(m, bc1), vu = fdiv(v, bc2);
+        const float denom = p.mode == 0 ? fsqrt(fadd(vu, eps)) : fadd(fsqrt(vu), eps);
+        const float upd = fadd(fdiv(mu, denom), fmul(decay, w));
+        w = fsub(w, fmul(p.lr, upd));
+        x[0] = w; x[1] = m; x[2] = v;
+        if constexpr (kCopy) x[4] = w;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// SGDFunctor: csrc/multi_tensor_sgd_kernel.cu:87-134.   lists: g, w, mom [, fp16 model copy]
+template <class Tg, class Tw, bool kCopy> struct SgdOp : OpBase {
+    static constexpr int kLists = kCopy ? 4 : 3;
+    template <int D> using T = typename Types<Tg, Tw, Tw, __half>::template at<D>;
+    static constexpr unsigned kRead = 0b0111, kWrite = kCopy ? 0b1110 : 0b0110;
+    static constexpr bool kEarlyExit = true;  // :46
+    struct Params { float wd, momentum, dampening, lr, scale; int nesterov, first_run, wd_after_momentum; };
+    Params p;
+    float omd, nlr;
+    __device__ explicit SgdOp(const Params& q) : p(q), omd(fsub(1.f, q.dampening)), nlr(-q.lr) {}
+    // The momentum buffer is only consumed when momentum != 0 and this is not the first run, and only
+    // written when momentum != 0 (:113-132): skip the traffic otherwise.
+    __device__ __forceinline__ bool load(int d) const { return d != 2 || (p.momentum != 0.f && !p.first_run); }
+    __device__ __forceinline__ bool store(int d) const { return d != 2 || p.momentum != 0.f; }
+    __device__ __forceinline__ void elem(float (&x)[kLists], State&) const {
+        float g = fmul(x[0], p.scale);
+        const float w = x[1];
+        float mom = x[2];
+        if (p.wd != 0.f && !p.wd_after_momentum) g = fadd(g, fmul(p.wd, w));
+        if (p.momentum != 0.f) {
+            if (!p.first_run) mom = fadd(fmul(mom, p.momentum), fmul(omd, g));
+            else mom = g;
+            if (p.nesterov) g = fadd(g, fmul(p.momentum, mom));
+            else g = mom;
+        }
+        if (p.wd != 0.f && p.wd_after_momentum) g = fadd(g, fmul(p.wd, w));
+        // weight_in[i] += (-lr * g): for a 16-bit T_weight the increment is rounded to T first (the only
+        // viable overload is operator+=(T&, const T&), torch/headeronly/util/Half.h:529), then T + T.
+        const float nw = fadd(w, Elem<Tw>::round(fmul(nlr, g)));
+        x[1] = nw;
+        x[2] = mom;
+        if constexpr (kCopy) x[3] = Elem<Tw>::round(nw);  // cast from the STORED weight (:130)
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Norm accumulation state: U independent accumulators are not needed for correctness; one per thread.
+struct SumState { float sum; };
+
+// L2NormFunctor: csrc/multi_tensor_l2norm_kernel.cu:56-107.  One tile == one reference chunk, so the flag
+// ("chunk partial sum is non-finite", :103-104) has the reference's granularity.   lists: x
+template <class Tx> struct L2NormOp : OpBase {
+    static constexpr int kLists = 1;
+    template <int D> using T = Tx;
+    static constexpr unsigned kRead = 0b1, kWrite = 0b0;
+    struct Params { float* partials; };
+    using State = SumState;
+    Params p;
+    __device__ explicit L2NormOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void init(State& s) const { s.sum = 0.f; }
+    __device__ __forceinline__ void elem(float (&x)[1], State& s) const { s.sum = fadd(s.sum, fmul(x[0], x[0])); }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+        const float tot = block_sum<THREADS>(s.sum, smem);
+        if (threadIdx.x == 0) {
+            p.partials[tile] = tot;
+            if (!finite_f(tot)) *noop = 1;
+        }
+        s.sum = 0.f;
+    }
+};
+
+// L2NormScaleFunctor: csrc/multi_tensor_l2norm_scale_kernel.cu:79-81,127-131.   lists: in, out
+template <class Tin, class Tout> struct L2NormScaleOp : OpBase {
+    static constexpr int kLists = 2;
+    template <int D> using T = typename Types<Tin, Tout>::template at<D>;
+    static constexpr unsigned kRead = 0b01, kWrite = 0b10;
+    struct Params { float* partials; float scale; };
+    using State = SumState;
+    Params p;
+    __device__ explicit L2NormScaleOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void init(State& s) const { s.sum = 0.f; }
+    __device__ __forceinline__ void elem(float (&x)[2], State& s) const {
+        s.sum = fadd(s.sum, fmul(x[0], x[0]));
+        x[1] = fmul(x[0], p.scale);
+    }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+        const float tot = block_sum<THREADS>(s.sum, smem);
+        if (threadIdx.x == 0) {
+            p.partials[tile] = tot;
+            if (!finite_f(tot)) *noop = 1;
+        }
+        s.sum = 0.f;
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// LAMB stage 1: csrc/multi_tensor_lamb.cu:66,121-143, fused with BOTH per-tensor norm passes of
+// multi_tensor_lamb_cuda (:370 ||p|| before the update, :394 ||u|| of the stored update): the per-tile
+// partial sums of p^2 and (T-rounded u)^2 are written to scratch and reduced per tensor by
+// lamb_norm_finalize_kernel.   lists: g (overwritten with u), p, m, v
+struct Sum2State { float sp, su; };
+template <class Tp> struct LambStage1Op : OpBase {
+    static constexpr int kLists = 4;
+    template <int D> using T = Tp;
+    static constexpr unsigned kRead = 0b1111, kWrite = 0b1101;
+    struct Params {
+        float beta1, beta2, beta3, bc1, bc2, eps, decay, max_grad_norm;
+        const float* global_grad_norm;
+        float* partials;      // [2][ntiles]: p^2 then u^2
+        uint32_t ntiles;
+        int mode, need_norms;
+    };
+    using State = Sum2State;
+    Params p;
+    float clip, omb2;
+    __device__ explicit LambStage1Op(const Params& q) : p(q), omb2(fsub(1.f, q.beta2)) {
+        const float gn = __ldg(q.global_grad_norm);
+        clip = gn > q.max_grad_norm ? fdiv(gn, q.max_grad_norm) : 1.0f;  // :66
+    }
+    __device__ __forceinline__ void init(State& s) const { s.sp = 0.f; s.su = 0.f; }
+    // p is only needed for the decay term (:102-103) or for its norm
+    __device__ __forceinline__ bool load(int d) const { return d != 1 || p.decay != 0.f || p.need_norms; }
+    __device__ __forceinline__ void elem(float (&x)[4], State& s) const {
+        const float w_in = x[1];
+        s.sp = fadd(s.sp, fmul(w_in, w_in));
+        const float w = p.decay == 0.f ? 0.f : w_in;  // r_p = 0 when decay == 0 (:123-128)
+        float m = x[2], v = x[3];
+        float sg = fdiv(x[0], clip);
+        if (p.mode == 0) sg = fadd(sg, fmul(p.decay, w));
+        m = fadd(fmul(m, p.beta1), fmul(p.beta3, sg));
+        v = fadd(fmul(v, p.beta2), fmul(fmul(omb2, sg), sg));
+        const float denom = fadd(fsqrt(fdiv(v, p.bc2)), p.eps);
+        float u = fdiv(fdiv(m, p.bc1), denom);
+        if (p.mode != 0) u = fadd(u, fmul(p.decay, w));
+        const float ur = Elem<Tp>::round(u);  // the reference norms the STORED update
+        s.su = fadd(s.su, fmul(ur, ur));
+        x[0] = u; x[2] = m; x[3] = v;
+    }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t*) const {
+        if (p.need_norms) {  // uniform
+            const float tp = block_sum<THREADS>(s.sp, smem);
+            const float tu = block_sum<THREADS>(s.su, smem);
+            if (threadIdx.x == 0) { p.partials[tile] = tp; p.partials[p.ntiles + tile] = tu; }
+        }
+        s.sp = 0.f; s.su = 0.f;
+    }
+};
+
+// LAMB stage 2: csrc/multi_tensor_lamb.cu:255-263,289.   lists: u, p
+template <class Tp> struct LambStage2Op : OpBase {
+    static constexpr int kLists = 2;
+    template <int D> using T = Tp;
+    static constexpr unsigned kRead = 0b11, kWrite = 0b10;
+    struct Params { const float *param_norm, *update_norm; float lr, decay; int use_nvlamb; };
+    Params p;
+    float ratio;
+    __device__ explicit LambStage2Op(const Params& q) : p(q), ratio(q.lr) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        ratio = p.lr;
+        if (p.use_nvlamb || p.decay != 0.0f) {
+            const float pn = p.param_norm[t], un = p.update_norm[t];  // plain loads: written by the previous kernel
+            ratio = (un != 0.0f && pn != 0.0f) ? fmul(p.lr, fdiv(pn, un)) : p.lr;
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[2], State&) const { x[1] = fsub(x[1], fmul(ratio, x[0])); }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Legacy split LAMB, arithmetic "in T": every value assigned to a T variable is rounded to T.
+// csrc/multi_tensor_lamb_stage_1.cu:81-100.   lists: g (Tg), p, m, v (Tp), update (Tu)
+template <class Tg, class Tp, class Tu> struct LambStage1LegacyOp : OpBase {
+    static constexpr int kLists = 5;
+    template <int D> using T = typename Types<Tg, Tp, Tp, Tp, Tu>::template at<D>;
+    static constexpr unsigned kRead = 0b01111, kWrite = 0b11100;
+    struct Params { const float* per_tensor_decay; float beta1, beta2, bc1, bc2, eps, clip; };
+    Params p;
+    float decay, omb1, omb2;
+    __device__ explicit LambStage1LegacyOp(const Params& q) : p(q), decay(0.f), omb1(fsub(1.f, q.beta1)), omb2(fsub(1.f, q.beta2)) {}
+    __device__ __forceinline__ void begin_tensor(int t) { decay = __ldg(p.per_tensor_decay + t); }
+    __device__ __forceinline__ void elem(float (&x)[5], State&) const {
+        using R = Elem<Tp>;
+        const float w = x[1];
+        float m = x[2], v = x[3];
+        const float sg = R::round(fdiv(x[0], p.clip));
+        m = R::round(fadd(fmul(m, p.beta1), fmul(omb1, sg)));
+        v = R::round(fadd(fmul(v, p.beta2), fmul(fmul(omb2, sg), sg)));
+        const float mu = R::round(fdiv(m, p.bc1)), vu = R::round(fdiv(v, p.bc2));
+        const float denom = R::round(fadd(fsqrt(vu), p.eps));
+        const float q = R::round(fdiv(mu, denom));  // T / T returns T
+        x[4] = R::round(fadd(q, fmul(decay, w)));
+        x[2] = m; x[3] = v;
+    }
+};
+
+// csrc/multi_tensor_lamb_stage_2.cu:41-47,77.   lists: p (Tp), update (Tu)
+template <class Tp, class Tu> struct LambStage2LegacyOp : OpBase {
+    static constexpr int kLists = 2;
+    template <int D> using T = typename Types<Tp, Tu>::template at<D>;
+    static constexpr unsigned kRead = 0b11, kWrite = 0b01;
+    struct Params { const float *param_norm, *update_norm; float lr, decay; int use_nvlamb; };
+    Params p;
+    float ratio;
+    __device__ explicit LambStage2LegacyOp(const Params& q) : p(q), ratio(q.lr) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        ratio = p.lr;
+        if (p.use_nvlamb || p.decay != 0.0f) {
+            const float pn = p.param_norm[t], un = p.update_norm[t];
+            ratio = (un != 0.0f && pn != 0.0f) ? fmul(p.lr, fdiv(pn, un)) : p.lr;
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[2], State&) const {
+        x[0] = fsub(x[0], fmul(ratio, Elem<Tp>::round(x[1])));
+    }
+};
+
+}  // namespace mt

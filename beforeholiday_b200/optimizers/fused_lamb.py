@@ -1,0 +1,111 @@
+"""FusedLAMB -- drop-in for apex.optimizers.FusedLAMB (/root/reference/apex/optimizers/fused_lamb.py:4-215).
+
+step(): global gradient norm over all groups (fp32 and fp16 lists, blended with a third l2norm call, exactly the
+reference's three ``multi_tensor_l2norm`` calls, fused_lamb.py:108-136), then one ``amp_C.multi_tensor_lamb`` call per
+dtype bucket per group.  The global norm stays on the device; the trust ratios are computed on the device.
+
+On B200 ``multi_tensor_lamb`` is 3 launches (stage 1 with both per-tensor norms accumulated in-pass, norm finalize,
+stage 2) instead of the reference's ~300 for BERT-large, and 44 B/param instead of 52.
+"""
+from __future__ import annotations
+
+import torch
+
+from ..multi_tensor_apply import multi_tensor_applier, multi_tensor_applier_l2norm
+
+
+class FusedLAMB(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, bias_correction=True, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01,
+                 amsgrad=False, adam_w_mode=True, grad_averaging=True, set_grad_none=True, max_grad_norm=1.0,
+                 use_nvlamb=False):
+        if amsgrad:
+            raise RuntimeError('FusedLAMB does not support the AMSGrad variant.')
+        defaults = dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps, weight_decay=weight_decay,
+                        grad_averaging=grad_averaging, max_grad_norm=max_grad_norm)
+        super().__init__(params, defaults)
+        if not (multi_tensor_applier.available and multi_tensor_applier_l2norm.available):
+            raise RuntimeError('beforeholiday_b200.optimizers.FusedLAMB requires the CUDA extension (no fallback)')
+        from .. import load_amp_C
+
+        amp_C = load_amp_C()
+        self.multi_tensor_l2norm = amp_C.multi_tensor_l2norm
+        self.multi_tensor_lamb = amp_C.multi_tensor_lamb
+        self._dummy_overflow_buf = torch.tensor([0], dtype=torch.int,
+                                                device=self.param_groups[0]["params"][0].device)
+        self.adam_w_mode = 1 if adam_w_mode else 0
+        self.set_grad_none = set_grad_none
+        self.use_nvlamb = use_nvlamb
+
+    def zero_grad(self, set_to_none=None):
+        if self.set_grad_none if set_to_none is None else set_to_none:
+            for group in self.param_groups:
+                for p in group['params']:
+                    p.grad = None
+        else:
+            super().zero_grad(set_to_none=False)
+
+    def _global_grad_norm(self):
+        g32, g16 = [], []
+        for group in self.param_groups:
+            for p in group['params']:
+                if p.grad is None:
+                    continue
+                if p.dtype == torch.float32:
+                    g32.append(p.grad.data)
+                elif p.dtype == torch.float16:
+                    g16.append(p.grad.data)
+                else:
+                    raise RuntimeError('FusedLAMB only support fp16 and fp32.')
+        device = self.param_groups[0]["params"][0].device
+        n32 = torch.zeros(1, device=device)
+        n16 = torch.zeros(1, device=device)
+        if g32:
+            n32 = multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g32], False)[0]
+        if g16:
+            n16 = multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g16], False)[0]
+        # blend: sqrt(n32^2 + n16^2), on the device
+        return multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [[n32, n16]], False)[0]
+
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            loss = closure()
+
+        global_grad_norm = self._global_grad_norm()
+        max_grad_norm = self.defaults['max_grad_norm']
+
+        for group in self.param_groups:
+            bias_correction = 1 if group['bias_correction'] else 0
+            beta1, beta2 = group['betas']
+            grad_averaging = 1 if group['grad_averaging'] else 0
+            group['step'] = group.get('step', 0) + 1
+
+            b16 = ([], [], [], [])
+            b32 = ([], [], [], [])
+            for p in group['params']:
+                if p.grad is None:
+                    continue
+                if p.grad.data.is_sparse:
+                    raise RuntimeError('FusedLAMB does not support sparse gradients, please consider SparseAdam instead')
+                state = self.state[p]
+                if len(state) == 0:
+                    state['exp_avg'] = torch.zeros_like(p.data)
+                    state['exp_avg_sq'] = torch.zeros_like(p.data)
+                if p.dtype == torch.float16:
+                    b = b16
+                elif p.dtype == torch.float32:
+                    b = b32
+                else:
+                    raise RuntimeError('FusedLAMB only support fp16 and fp32.')
+                b[0].append(p.grad.data)
+                b[1].append(p.data)
+                b[2].append(state['exp_avg'])
+                b[3].append(state['exp_avg_sq'])
+
+            for g, w, m, v in (b16, b32):
+                if g:
+                    multi_tensor_applier(self.multi_tensor_lamb, self._dummy_overflow_buf, [g, w, m, v],
+                                         group['lr'], beta1, beta2, group['eps'], group['step'], bias_correction,
+                                         group['weight_decay'], grad_averaging, self.adam_w_mode, global_grad_norm,
+                                         max_grad_norm, self.use_nvlamb)
+        return loss

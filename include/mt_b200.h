@@ -1,0 +1,155 @@
+/*
+ * mt_b200.h -- C ABI of libmt_b200.so: the B200 (sm_100a) multi-tensor-apply optimizer path.
+ *
+ * This is the drop-in boundary for the reference's `amp_C` pybind module
+ * (/root/reference/csrc/amp_C_frontend.cpp:165-194).  Every entry point below replaces one
+ * `*_cuda()` host function of the reference and keeps its argument meaning; torch types are
+ * replaced by plain pointers and sizes (MtTensorLists).  The pybind module `amp_C` shipped in
+ * beforeholiday_b200/csrc/amp_C_module.cpp is a thin adaptor over this header; INTEGRATION.md
+ * shows the binding a maintainer of the reference would write.
+ *
+ * Conventions
+ *   - All pointers inside MtTensorLists, `noop_flag`, norm outputs and scratch are DEVICE pointers on
+ *     `tl->device`.  Tensors are dense (any memory format: the op runs over physical order, as
+ *     /root/reference/csrc/multi_tensor_apply.cuh:64-68 allows).
+ *   - Calls enqueue work on `stream` (a cudaStream_t) and return; no synchronisation.
+ *   - Return value: 0 on success, a negative MT_E* code otherwise; mt_last_error() returns a
+ *     thread-local message (the pybind layer raises RuntimeError with it, mirroring TORCH_CHECK).
+ *   - `chunk_size` is accepted for signature compatibility.  It only has semantic meaning for the
+ *     norm ops, where the overflow flag is defined per chunk (see mt_multi_tensor_l2norm).
+ *   - dtype tags: MT_F32, MT_F16, MT_BF16, MT_F64.
+ *   - There is no CPU fallback: on a machine without a CUDA device every compute entry point
+ *     returns MT_ECUDA.
+ */
+#ifndef MT_B200_H_
+#define MT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MT_MAX_DEPTH 5
+
+enum { MT_F32 = 0, MT_F16 = 1, MT_BF16 = 2, MT_F64 = 3 };
+
+enum {
+    MT_OK = 0,
+    MT_EINVAL = -1,   /* bad argument (depth, dtype combination, null pointer, size mismatch) */
+    MT_ECUDA = -2,    /* a CUDA runtime call failed (message has the cudaError string) */
+    MT_ECAPTURE = -3, /* device-table cache miss while the stream is being captured: run one eager warm-up call first */
+    MT_ESCRATCH = -4  /* scratch buffer missing or too small */
+};
+
+/* `depth` lists of `ntensors` tensors; replaces std::vector<std::vector<at::Tensor>>
+ * (/root/reference/csrc/multi_tensor_apply.cuh:44-72).  ptrs is list-major: ptrs[d * ntensors + t].
+ * numel[t] is shared by all lists (the reference checks numel equality, :70).  Empty tensors are legal. */
+typedef struct MtTensorLists {
+    int32_t depth;
+    int32_t device;              /* CUDA device ordinal that owns every pointer */
+    int64_t ntensors;
+    const void* const* ptrs;
+    const int64_t* numel;
+    int32_t dtype[MT_MAX_DEPTH]; /* per-list dtype tag */
+} MtTensorLists;
+
+const char* mt_last_error(void);
+const char* mt_version(void);
+
+/* out = float(in) * scale; *noop_flag = 1 iff any input element is non-finite.
+ * Lists: [in, out], any of f32/f16/bf16 each.
+ * Replaces multi_tensor_scale_cuda, /root/reference/csrc/multi_tensor_scale_kernel.cu:113-136. */
+int mt_multi_tensor_scale(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float scale, void* stream);
+
+/* out = a*float(x) + b*float(y); finite check on x (arg_to_check 0), y (1) or both (-1).
+ * Lists: [x, y, out], any of f32/f16/bf16 each.
+ * Replaces multi_tensor_axpby_cuda, /root/reference/csrc/multi_tensor_axpby_kernel.cu:128-157. */
+int mt_multi_tensor_axpby(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float a, float b,
+                          int arg_to_check, void* stream);
+
+/* Bytes of scratch the norm / LAMB entry points need for these lists and this chunk size. */
+size_t mt_norm_scratch_bytes(int chunk_size, const MtTensorLists* tl);
+size_t mt_lamb_scratch_bytes(int chunk_size, const MtTensorLists* tl);
+
+/* ret[0] = ||all tensors||_2 ; ret_per_tensor[t] = ||tensor t||_2 (when per_tensor != 0).
+ * *noop_flag = 1 iff the sum of squares of any `chunk_size`-element chunk of any tensor is non-finite
+ * (the reference's definition, csrc/multi_tensor_l2norm_kernel.cu:103-104).  Lists: [x], f32/f16/bf16.
+ * scratch: mt_norm_scratch_bytes() bytes of device memory, contents irrelevant on entry.
+ * Replaces multi_tensor_l2norm_cuda + cleanup, /root/reference/csrc/multi_tensor_l2norm_kernel.cu:198-237,301-364. */
+int mt_multi_tensor_l2norm(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
+                           float* ret, float* ret_per_tensor, void* scratch, size_t scratch_bytes, void* stream);
+
+/* As mt_multi_tensor_l2norm over list 0 and additionally out = float(in) * scale into list 1.
+ * Lists: [in, out], f32/f16 in the reference; bf16 is accepted too.
+ * Replaces multi_tensor_l2norm_scale_cuda, /root/reference/csrc/multi_tensor_l2norm_scale_kernel.cu:258-324. */
+int mt_multi_tensor_l2norm_scale(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float scale,
+                                 int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
+                                 size_t scratch_bytes, void* stream);
+
+/* Adam (mode 0, L2) / AdamW (mode 1).  Lists: [g, p, m, v], one dtype for all four (f32/f16/bf16/f64),
+ * fp32 math; bias corrections evaluated on the host in double and rounded to float.  The noop flag is
+ * ignored, as in the reference.
+ * Replaces multi_tensor_adam_cuda, /root/reference/csrc/multi_tensor_adam.cu:129-171. */
+int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float lr, float beta1,
+                         float beta2, float epsilon, int step, int mode, int bias_correction, float weight_decay,
+                         void* stream);
+
+/* SGD with momentum / nesterov / dampening / weight decay, fused gradient scale, optional fp16 model copy.
+ * Lists: [g, w, mom] or [g, w, mom, w_fp16]; dtype combinations as the reference's six cases.
+ * Does nothing when *noop_flag != 0 (device-side test).
+ * Replaces multi_tensor_sgd_cuda, /root/reference/csrc/multi_tensor_sgd_kernel.cu:141-322. */
+int mt_multi_tensor_sgd(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float wd, float momentum,
+                        float dampening, float lr, int nesterov, int first_run, int wd_after_momentum, float scale,
+                        void* stream);
+
+/* LAMB.  Lists: [g, p, m, v], one dtype (f32/f16/bf16).  global_grad_norm is a DEVICE float[1]; the trust
+ * ratios are computed on the device.  g is overwritten with the update, as in the reference.
+ * scratch: mt_lamb_scratch_bytes() bytes.
+ * Replaces multi_tensor_lamb_cuda, /root/reference/csrc/multi_tensor_lamb.cu:332-413. */
+int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float lr, float beta1,
+                         float beta2, float epsilon, int step, int bias_correction, float weight_decay,
+                         int grad_averaging, int mode, const float* global_grad_norm, float max_grad_norm,
+                         int use_nvlamb, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Legacy split LAMB.  stage1 lists: [g, p, m, v, update]; per_tensor_decay is a DEVICE float[ntensors];
+ * clipped_global_grad_norm is passed by value (the reference reads the norm on the host,
+ * csrc/multi_tensor_lamb_stage_1.cu:126-127).  Arithmetic is carried out in the parameter dtype.
+ * Replaces multi_tensor_lamb_stage1_cuda / stage2_cuda,
+ * /root/reference/csrc/multi_tensor_lamb_stage_1.cu:112-151, multi_tensor_lamb_stage_2.cu:94-125. */
+int mt_multi_tensor_lamb_stage1(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                const float* per_tensor_decay, int step, float beta1, float beta2, float epsilon,
+                                float global_grad_norm, float max_global_grad_norm, void* stream);
+int mt_multi_tensor_lamb_stage2(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                const float* per_tensor_param_norm, const float* per_tensor_update_norm, float lr,
+                                float weight_decay, int use_nvlamb, void* stream);
+
+/* Mixed-precision (sharded) Adam: fp32 p, m, v; 16- or 32-bit g; optional p_copy in g's dtype.
+ * Lists: [p, m, v, g] or [p, m, v, g, p_copy].  Per-tensor hyper-parameters are DEVICE arrays of ntensors.
+ * g is divided by grad_scale.  mode 0: eps inside the square root, mode 1: outside.
+ * honour_noop != 0: do nothing when *noop_flag != 0 (extension: lets a fused overflow check skip the step
+ * without a host round trip; the reference ignores the flag).
+ * Replaces multi_tensor_fused_adam_cuda,
+ * /root/reference/apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:169-228. */
+int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                               const float* per_tensor_beta1, const float* per_tensor_beta2,
+                               const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                               const float* per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
+                               int honour_noop, void* stream);
+
+/* Device-table cache introspection (the table replaces the by-value TensorListMetadata kernel argument,
+ * /root/reference/csrc/multi_tensor_apply.cuh:19-26). */
+typedef struct MtCacheStats {
+    uint64_t hits, misses, uploads_bytes, entries, device_bytes;
+} MtCacheStats;
+int mt_table_cache_stats(int device, MtCacheStats* out);
+int mt_table_cache_clear(int device);
+
+/* Launch counter: number of kernels this library has launched since load (all devices). */
+uint64_t mt_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MT_B200_H_ */

@@ -1,0 +1,233 @@
+"""Pin the CPU oracle (oracle/mt_oracle.c) before anything trusts it.
+
+Pins, in order of authority:
+  1. the known answers of the reference's own unit tests (scale -> 1.0, axpby -> 136.0, l2norm -> torch.norm, the
+     nan/inf flag semantics): /root/reference/tests/L0/run_amp/test_multi_tensor_{scale,axpby,l2norm}.py;
+  2. outputs of the reference's own CPU-capable Python (apex/amp/scaler.py fallbacks, RefLAMB from the reference's
+     test_lamb.py) stored in tests/golden/ref_cpu.pt by tests/golden/make_golden_cpu.py;
+  3. torch.optim.Adam/AdamW/SGD trajectories -- the oracle the reference's optimizer tests use
+     (tests/L0/run_optimizers/test_fused_optimizer.py), same fixture file;
+  4. (GPU box) golden vectors from the reference's CUDA kernels: tests/test_gpu_vs_reference.py.
+All run on CPU (`-m "not gpu"`).
+"""
+import itertools
+from pathlib import Path
+
+import pytest
+import torch
+
+from util import bits_equal, max_rel, rel_close
+
+GOLD = torch.load(Path(__file__).parent / "golden" / "ref_cpu.pt", weights_only=False)
+N, ITERS = GOLD["N"], GOLD["ITERS"]
+
+
+def gen_inputs(seed, n, dtype=torch.float32, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(n, generator=g) * scale).to(dtype)
+
+
+def flag():
+    return torch.zeros(1, dtype=torch.int32)
+
+
+# ---------------------------------------------------------------------------------------- 1. reference KATs
+DTYPES3 = [torch.float32, torch.float16, torch.bfloat16]
+
+
+@pytest.mark.parametrize("in_t,out_t", list(itertools.product(DTYPES3, DTYPES3)))
+@pytest.mark.parametrize("sizea,sizeb", [(7777, 555), (777, 555), (555, 2048 * 32 + 1), (555, 333)])
+def test_scale_kat(oracle, in_t, out_t, sizea, sizeb):
+    # test_multi_tensor_scale.py:36-56: fill 4.0, scale 1/4 -> exactly 1.0, flag stays 0
+    ins = [torch.full((sizea,), 4.0, dtype=in_t), torch.full((sizeb,), 4.0, dtype=in_t)]
+    outs = [torch.zeros(sizea, dtype=out_t), torch.zeros(sizeb, dtype=out_t)]
+    f = flag()
+    oracle.multi_tensor_scale(2048 * 32, f, [ins, outs], 1.0 / 4.0)
+    assert all(bool((o == 1.0).all()) for o in outs)
+    assert f.item() == 0
+    # :119-124: nan at [0][0], inf at the end of the last tensor -> flag
+    for t, i, val in ((0, 0, float("nan")), (1, sizeb - 1, float("inf")), (0, sizea // 2, float("-inf"))):
+        bad = [x.clone() for x in ins]
+        bad[t][i] = val
+        f = flag()
+        oracle.multi_tensor_scale(2048 * 32, f, [bad, outs], 1.0 / 4.0)
+        assert f.item() == 1
+
+
+@pytest.mark.parametrize("x_t,y_t,o_t", list(itertools.product(DTYPES3, DTYPES3, DTYPES3)))
+def test_axpby_kat(oracle, x_t, y_t, o_t):
+    # test_multi_tensor_axpby.py:39,75-80: a=2, b=8, x=4, y=16 -> 136.0 in every dtype
+    n = 7777
+    x, y, o = torch.full((n,), 4.0, dtype=x_t), torch.full((n,), 16.0, dtype=y_t), torch.zeros(n, dtype=o_t)
+    f = flag()
+    oracle.multi_tensor_axpby(2048 * 32, f, [[x], [y], [o]], 2.0, 8.0, -1)
+    assert bool((o == 136.0).all()) and f.item() == 0
+    for which, arg, expect in (("x", 0, 1), ("x", 1, 0), ("y", 1, 1), ("y", 0, 0), ("x", -1, 1), ("y", -1, 1)):
+        xb, yb = x.clone(), y.clone()
+        (xb if which == "x" else yb)[n // 3] = float("inf")
+        f = flag()
+        oracle.multi_tensor_axpby(2048 * 32, f, [[xb], [yb], [o]], 2.0, 8.0, arg)
+        assert f.item() == expect, (which, arg)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.float16])
+@pytest.mark.parametrize("chunk", [2048 * 32, 333, 33333])
+@pytest.mark.parametrize("per_tensor", [False, True])
+def test_l2norm_kat(oracle, dt, chunk, per_tensor):
+    # test_multi_tensor_l2norm.py:35-56: constant 4.0, allclose to torch.norm (global and per tensor), flag 0
+    sizes = [7777, 555, 2048 * 32 + 1]
+    xs = [torch.full((n,), 4.0, dtype=dt) for n in sizes]
+    f = flag()
+    norm, norm_pt = oracle.multi_tensor_l2norm(chunk, f, [xs], per_tensor)
+    ref = torch.cat([x.float() for x in xs]).norm()
+    assert torch.allclose(norm, ref.reshape(1))
+    if per_tensor:
+        assert torch.allclose(norm_pt, torch.stack([x.float().norm() for x in xs]))
+    assert f.item() == 0
+    # random data against a float64 sum: the north-star tolerance for norms is 1e-5 relative
+    xs = [gen_inputs(5 + i, n, dt) for i, n in enumerate(sizes)]
+    norm, norm_pt = oracle.multi_tensor_l2norm(chunk, f, [xs], True)
+    assert max_rel(norm, torch.cat([x.double() for x in xs]).norm().reshape(1)) < 1e-5
+    assert max_rel(norm_pt, torch.stack([x.double().norm() for x in xs])) < 1e-5
+
+
+def test_l2norm_flag_is_per_chunk_partial(oracle):
+    # the flag is raised by a non-finite CHUNK PARTIAL (l2norm_kernel.cu:103-104): finite inputs whose squares
+    # overflow fp32 trip it, and a finite global overflow of finite partials does not.
+    x = torch.full((1000,), 3e19, dtype=torch.float32)  # x^2 = 9e38 > FLT_MAX
+    f = flag()
+    oracle.multi_tensor_l2norm(65536, f, [[x]], False)
+    assert f.item() == 1
+    y = torch.full((8,), 1.5e19, dtype=torch.float32)  # each chunk (1 element): 2.25e38, finite; the sum is not
+    f = flag()
+    n, _ = oracle.multi_tensor_l2norm(1, f, [[y]], False)
+    assert f.item() == 0 and torch.isinf(n).all()
+
+
+def test_l2norm_scale(oracle):
+    x = gen_inputs(3, 70001)
+    o = torch.zeros_like(x, dtype=torch.float16)
+    f = flag()
+    n, npt = oracle.multi_tensor_l2norm_scale(65536, f, [[x], [o]], 0.5, True)
+    assert bits_equal(o, (x * 0.5).half())
+    assert max_rel(n, x.double().norm().reshape(1)) < 1e-5 and max_rel(npt, x.double().norm().reshape(1)) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------- 2. reference python
+def test_scale_python_fallback_golden(oracle):
+    for case in GOLD["scale_python"]:
+        model = gen_inputs(11, N, case["in_dtype"], 3.0)
+        if case["inject"] == "inf":
+            model[N // 2] = float("inf")
+        if case["inject"] == "nan":
+            model[-1] = float("nan")
+        master = torch.zeros(N, dtype=torch.float32)
+        f = flag()
+        oracle.multi_tensor_scale(65536, f, [[model], [master]], 1.0 / 65536.0)
+        assert bool(f.item()) == case["overflow"]
+        if not case["overflow"]:  # the python fallback returns before writing on overflow
+            assert bits_equal(master, case["master"])
+
+
+def test_axpby_python_fallback_golden(oracle):
+    for case in GOLD["axpby_python"]:
+        model = gen_inputs(12, N, torch.float16, 2.0)
+        if case["inject"] == "inf":
+            model[7] = float("inf")
+        stashed = gen_inputs(13, N, torch.float32)
+        master = torch.zeros(N, dtype=torch.float32)
+        f = flag()
+        oracle.multi_tensor_axpby(65536, f, [[model], [stashed], [master]], 1.0 / 128.0, 1.0, 0)
+        assert bool(f.item()) == case["overflow"]
+        if not case["overflow"]:
+            assert bits_equal(master, case["master"])
+
+
+@pytest.mark.parametrize("wd", [0.0, 0.01])
+def test_lamb_vs_reflamb_golden(oracle, wd):
+    # FusedLAMB(use_nvlamb=True) is what the reference test pairs with RefLAMB (test_lamb.py:163-170)
+    gold = GOLD["ref_lamb"][wd]
+    sizes = gold["sizes"]
+    ps = [gen_inputs(100 + i, n).abs() * 0.5 + 0.01 for i, n in enumerate(sizes)]
+    ms = [torch.zeros(n) for n in sizes]
+    vs = [torch.zeros(n) for n in sizes]
+    f = flag()
+    for it in range(ITERS):
+        gs = [gen_inputs(1000 + 10 * it + i, n) * 0.1 for i, n in enumerate(sizes)]
+        gnorm, _ = oracle.multi_tensor_l2norm(65536, f, [gs], False)
+        oracle.multi_tensor_lamb(8192, f, [gs, ps, ms, vs], 5e-4, 0.9, 0.999, 1e-6, it + 1, 1, wd, 1, 1, gnorm, 1.0, True)
+    for p, gp in zip(ps, gold["params"]):
+        # reference test tolerance: max_abs_diff 1e-3 (test_lamb.py:149); the two LAMBs differ only by rounding
+        assert (p - gp).abs().max() <= 1e-3
+        assert rel_close(p, gp, 2e-5, 1e-7)
+    for m, gm in zip(ms, gold["m"]):
+        assert rel_close(m, gm, 1e-5, 1e-7)  # moments are signed sums: atol covers cancellation
+
+
+# ---------------------------------------------------------------------------------------- 3. torch.optim
+def _run_oracle_adam(oracle, mode, wd):
+    torch.manual_seed(9876)
+    p = torch.rand(N)
+    m, v = torch.zeros(N), torch.zeros(N)
+    for it in range(ITERS):
+        g = gen_inputs(2000 + it, N).abs() % 1.0
+        oracle.multi_tensor_adam(8192, flag(), [[g], [p], [m], [v]], 5e-4, 0.9, 0.999, 1e-8, it + 1, mode, 1, wd)
+    return p
+
+
+@pytest.mark.parametrize("name,mode,wd", [("adam_l2", 0, 0.0), ("adam_l2_wd", 0, 0.1), ("adamw", 1, 0.01)])
+def test_adam_vs_torch_optim_golden(oracle, name, mode, wd):
+    p = _run_oracle_adam(oracle, mode, wd)
+    gold = GOLD["torch_optim"][name]
+    assert (p - gold).abs().max() <= 1e-3                 # the reference's own bound (test_fused_optimizer.py:13)
+    assert rel_close(p, gold, 1e-6, 2e-7)                 # north-star: 1e-6 relative (atol covers params near 0)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("sgd_mom", dict(lr=0.25, momentum=0.125, wd=0.0, nesterov=False)),
+    ("sgd_nesterov_wd", dict(lr=0.1, momentum=0.9, wd=1e-4, nesterov=True)),
+])
+def test_sgd_vs_torch_optim_golden(oracle, name, kw):
+    torch.manual_seed(9876)
+    p = torch.rand(N)
+    mom = torch.zeros(N)
+    for it in range(ITERS):
+        g = gen_inputs(2000 + it, N).abs() % 1.0
+        oracle.multi_tensor_sgd(8192, flag(), [[g], [p], [mom]], kw["wd"], kw["momentum"], 0.0, kw["lr"], kw["nesterov"],
+                                it == 0, False, 1.0)
+    gold = GOLD["torch_optim"][name]
+    assert rel_close(p, gold, 1e-6, 2e-7)
+
+
+def test_sgd_noop_skips(oracle):
+    p0 = gen_inputs(1, 1000)
+    p, mom, g = p0.clone(), torch.zeros(1000), gen_inputs(2, 1000)
+    f = torch.ones(1, dtype=torch.int32)
+    oracle.multi_tensor_sgd(8192, f, [[g], [p], [mom]], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0)
+    assert bits_equal(p, p0) and bool((mom == 0).all())
+
+
+def test_sgd_fp16_master_copy(oracle):
+    # case 3 (fp16 grad, fp32 master, fp16 model copy): the copy is the rounded master
+    g, w, mom = gen_inputs(1, 999, torch.float16), gen_inputs(2, 999), torch.zeros(999)
+    out = torch.zeros(999, dtype=torch.float16)
+    oracle.multi_tensor_sgd(8192, flag(), [[g], [w], [mom], [out]], 1e-4, 0.9, 0.0, 0.1, False, True, False, 1.0 / 128)
+    assert bits_equal(out, w.half())
+
+
+def test_dist_adam_matches_adamw_and_copy(oracle):
+    # DistAdamFunctor mode 1 == AdamW on fp32 masters with bf16 grads; p_copy is the rounded master
+    n = 5001
+    p = gen_inputs(1, n) * 0.02
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.AdamW([ref], lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    m, v = torch.zeros(n), torch.zeros(n)
+    pc = torch.zeros(n, dtype=torch.bfloat16)
+    for it in range(3):
+        g = gen_inputs(50 + it, n, torch.bfloat16, 1e-3 * 1024)
+        ref.grad = g.float() / 1024
+        opt.step()
+        oracle.multi_tensor_fused_adam(8192, flag(), [[p], [m], [v], [g], [pc]], [0.9], [0.95], [1], [1e-8], [0.1], 1e-3,
+                                       1024.0, it + 1, 1)
+    assert rel_close(p, ref.data, 1e-6, 1e-8)
+    assert bits_equal(pc, p.bfloat16())
