@@ -1,0 +1,145 @@
+"""World-size-2 tests of the sharded optimizer's HOST logic on CPU (gloo): layout, fragment ownership, and the
+reduce-scatter -> shard update -> all-gather orchestration.  The shard update itself is CUDA-only in the product;
+here it is replaced by the CPU oracle (test infrastructure) through the class's overridable hooks, so what is under
+test is everything around the kernel."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam, FlatLayout
+
+SIZES = [1000, 7, 4096, 33333, 1, 129]
+
+
+def test_layout_partitions_flat_space_exactly():
+    for world in (1, 2, 4, 8):
+        lay0 = FlatLayout(SIZES, world, 0, elem_bytes=2, bucket_cap_elems=8192)
+        assert lay0.padded % (world * 1024) == 0 and lay0.padded >= lay0.total
+        assert all(o % 64 == 0 for o in lay0.offsets)  # 128-byte aligned bf16 offsets
+        covered = torch.zeros(lay0.padded, dtype=torch.int32)
+        elems = 0
+        for r in range(world):
+            lay = FlatLayout(SIZES, world, r, elem_bytes=2, bucket_cap_elems=8192)
+            for b in range(lay.nbuckets):
+                lo, hi = lay.owned_range(b)
+                covered[lo:hi] += 1
+            for f in lay.fragments():
+                n = f.flat_hi - f.flat_lo
+                assert n > 0 and lay.offsets[f.param] + f.param_lo == f.flat_lo
+                olo, ohi = lay.owned_range(f.bucket)
+                assert olo <= f.flat_lo and f.flat_hi <= ohi
+                assert f.state_lo == f.bucket * lay.sub_shard + (f.flat_lo - olo)
+                elems += n
+        assert bool((covered == 1).all())          # every flat element owned by exactly one rank
+        assert elems == sum(SIZES)                 # every parameter element lands in exactly one fragment
+
+
+class CpuShardedAdam(DistributedFusedAdam):
+    """gloo + oracle stand-ins for the NCCL collectives and the CUDA update."""
+
+    def _init_comm(self):
+        self.rs_group = self.ag_group = self.group
+        self.rs_stream = self.ag_stream = None
+
+    def _reduce_scatter(self, b):
+        lo, hi = self.layout.bucket_range(b)
+        buf = self.grads_flat[lo:hi].float()
+        dist.all_reduce(buf, group=self.group)
+        olo, ohi = self.layout.owned_range(b)
+        self.grads_flat[olo:ohi].copy_(buf[olo - lo:ohi - lo])  # only the owned sub-shard is defined afterwards
+
+    def _all_gather(self, b):
+        lo, hi = self.layout.bucket_range(b)
+        olo, ohi = self.layout.owned_range(b)
+        parts = [torch.empty(self.layout.sub_shard, dtype=torch.float32) for _ in range(self.world)]
+        dist.all_gather(parts, self.params_flat[olo:ohi].float().contiguous(), group=self.group)
+        self.params_flat[lo:hi].copy_(torch.cat(parts))
+
+    def _update_bucket(self, b, grad_scale):
+        from oracle import mt_oracle as O
+
+        lists, hp = self._per_bucket[b]
+        if lists[0]:
+            O.multi_tensor_fused_adam(8192, self.noop, lists, *[h.tolist() for h in hp], self.lr, grad_scale,
+                                      self.step_count, 1 if self.adam_w_mode else 0, honour_noop=True)
+
+
+def _worker(rank, world, port, outdir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        full = [torch.randn(n) * 0.02 for n in SIZES]
+        wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
+        opt = CpuShardedAdam(numels=SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0, device="cpu",
+                             grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16, bucket_cap_mb=8192 * 2 / 2 ** 20,
+                             per_param_weight_decay=wds)
+        L = opt.layout
+        assert L.nbuckets > 1
+        for p, o in zip(full, L.offsets):
+            opt.params_flat[o:o + p.numel()].copy_(p)
+        opt.init_master_from_params()
+        for it in range(3):
+            # every rank contributes its own gradient; the step averages them
+            g = torch.Generator().manual_seed(100 * it + rank)
+            for n, o in zip(SIZES, L.offsets):
+                opt.grads_flat[o:o + n].copy_(torch.randn(n, generator=g) * 1e-2)
+            opt.step()
+        out = [opt.params_flat[o:o + n].clone() for n, o in zip(SIZES, L.offsets)]
+        torch.save(out, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.timeout(300)
+def test_sharded_step_world2_matches_single_process(tmp_path):
+    world = 2
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    results = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
+    # every rank ends with the same full bf16 parameters
+    for a, b in zip(results[0], results[1]):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+    # single-process replay with the oracle: bf16 master init, summed bf16 grads / world
+    from oracle import mt_oracle as O
+
+    torch.manual_seed(0)
+    full = [(torch.randn(n) * 0.02) for n in SIZES]
+    p32 = [p.bfloat16().float() for p in full]
+    m = [torch.zeros(n) for n in SIZES]
+    v = [torch.zeros(n) for n in SIZES]
+    pc = [torch.zeros(n, dtype=torch.bfloat16) for n in SIZES]
+    wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
+    k = len(SIZES)
+    for it in range(3):
+        gs = []
+        for n in SIZES:
+            gs.append(torch.zeros(n))
+        for r in range(world):
+            g = torch.Generator().manual_seed(100 * it + r)
+            for i, n in enumerate(SIZES):
+                gs[i] += (torch.randn(n, generator=g) * 1e-2).bfloat16().float()
+        gs = [x.bfloat16() for x in gs]
+        O.multi_tensor_fused_adam(8192, torch.zeros(1, dtype=torch.int32), [p32, m, v, gs, pc], [0.9] * k, [0.95] * k,
+                                  [1] * k, [1e-8] * k, wds, 1e-2, float(world), it + 1, 1)
+    for a, b in zip(results[0], pc):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))

@@ -181,7 +181,7 @@ def test_l2norm_flag_semantics(amp_C, oracle):
             x = torch.full((8,), 1.5e19)
             chunk = 1
         (ng, _), (nc, _) = run_both(amp_C, oracle, "multi_tensor_l2norm", [[x]], (False,), chunk=chunk)
-        assert bits_equal(ng.isfinite(), nc.isfinite())
+        assert bool(ng.isfinite().cpu().item()) == bool(nc.isfinite().item())
 
 
 @pytest.mark.parametrize("in_t,out_t", [(F32, F32), (F16, F32), (F32, F16), (F16, F16)])
