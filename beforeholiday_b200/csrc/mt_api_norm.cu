@@ -1,6 +1,6 @@
 // mt_api_norm.cu -- multi_tensor_l2norm / multi_tensor_l2norm_scale entry points and the norm finalize kernel.
 //
-// Pass 1 (persistent grid, one tile == one reference chunk): per-tile sum of squares -> scratch partials[tile],
+// Pass 1 (table-driven grid, one tile == one reference chunk): per-tile sum of squares -> scratch partials[tile],
 // flag raised when a tile's partial is non-finite (the reference's per-chunk definition,
 // /root/reference/csrc/multi_tensor_l2norm_kernel.cu:103-104).
 // Pass 2 (norm_finalize_kernel): fixed-order reduction of the partials -> global norm and per-tensor norms.
@@ -80,19 +80,19 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
         return set_error(MT_ESCRATCH, "%s: scratch too small (%zu < %zu bytes)", who, scratch_bytes, need);
     float* partials = static_cast<float*>(scratch);
     // 2 groups in flight per thread: a pure reduction has registers to spare
-    constexpr int G = 8, U = 2, THREADS = 512, MINB = 2;
+    constexpr int G = 8, U = 2, THREADS = 256, MINB = 4;
     if (depth == 1) {
         MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
             using Op = L2NormOp<Tx>;
             typename Op::Params prm{partials};
-            rc = launch_persistent<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+            rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
         })
     } else {
         MT_DISPATCH_FHB(tl->dtype[0], Tin, who,
             MT_DISPATCH_FHB(tl->dtype[1], Tout, who, {
                 using Op = L2NormScaleOp<Tin, Tout>;
                 typename Op::Params prm{partials, scale};
-                rc = launch_persistent<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             }))
     }
     if (rc) return rc;

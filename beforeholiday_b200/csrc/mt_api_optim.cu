@@ -6,8 +6,6 @@
 
 namespace mt {
 
-constexpr int kG = 8, kU = 1, kThreads = 512, kMinBlocks = 2;
-
 int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
                          int device, cudaStream_t stream);  // mt_api_norm.cu
 
@@ -65,7 +63,7 @@ extern "C" int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const Mt
     {                                                                                                     \
         using Op = AdamOp<CT>;                                                                            \
         typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay, mode};                 \
-        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+        return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
     }
     switch (tl->dtype[0]) {
         case MT_F32: MT_ADAM(float)
@@ -100,7 +98,7 @@ extern "C" int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, co
         using Op = DistAdamOp<TG, COPY, HN>;                                                              \
         typename Op::Params prm{per_tensor_beta1, per_tensor_beta2, per_tensor_eps, per_tensor_weight_decay, \
                                 per_tensor_bias_correction, lr, grad_scale, step, mode};                  \
-        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+        return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
     }
     MT_DISPATCH_FHB(tl->dtype[3], Tg, "multi_tensor_fused_adam", {
         if (copy) { if (honour_noop) MT_DADAM(Tg, true, true) else MT_DADAM(Tg, true, false) }
@@ -126,7 +124,7 @@ extern "C" int mt_multi_tensor_sgd(int chunk_size, int32_t* noop_flag, const MtT
     {                                                                                                     \
         using Op = SgdOp<TG, TW, COPY>;                                                                   \
         typename Op::Params prm{wd, momentum, dampening, lr, scale, nesterov, first_run, wd_after_momentum}; \
-        return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+        return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
     }
     // the reference's six combinations, /root/reference/csrc/multi_tensor_sgd_kernel.cu:165-314
     if (gt == MT_F16 && wt == MT_F16 && tl->depth == 3) MT_SGD(__half, __half, false)
@@ -180,7 +178,7 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
         using Op1 = LambStage1Op<Tp>;
         typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
                                 global_grad_norm, partials, tb.ntiles, mode, need_norms};
-        rc = launch_persistent<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+        rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
         if (rc) return rc;
         if (need_norms) {
             rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream);
@@ -189,7 +187,7 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
         // stage 2 walks lists [u (= g), p] of the SAME table: list indices 0 and 1
         using Op2 = LambStage2Op<Tp>;
         typename Op2::Params p2{pnorm, unorm, lr, weight_decay, use_nvlamb};
-        return launch_persistent<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);
+        return launch_table_kernel<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);
     })
     return MT_OK;
 }
@@ -216,7 +214,7 @@ extern "C" int mt_multi_tensor_lamb_stage1(int chunk_size, int32_t* noop_flag, c
             MT_DISPATCH_FHB(tl->dtype[4], Tu, "lamb_stage_1", {
                 using Op = LambStage1LegacyOp<Tg, Tp, Tu>;
                 typename Op::Params prm{per_tensor_decay, beta1, beta2, bc1, bc2, epsilon, clip};
-                return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+                return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
             })))
     return MT_OK;
 }
@@ -234,7 +232,7 @@ extern "C" int mt_multi_tensor_lamb_stage2(int chunk_size, int32_t* noop_flag, c
         MT_DISPATCH_FHB(tl->dtype[1], Tu, "lamb_stage_2", {
             using Op = LambStage2LegacyOp<Tp, Tu>;
             typename Op::Params prm{per_tensor_param_norm, per_tensor_update_norm, lr, weight_decay, use_nvlamb};
-            return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
         }))
     return MT_OK;
 }

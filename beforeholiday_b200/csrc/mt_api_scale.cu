@@ -2,12 +2,6 @@
 #include "mt_host.h"
 #include "mt_ops.cuh"
 
-namespace mt {
-// Launch shape shared by the element-wise families: 512 threads, 2 CTAs/SM (<= 64 registers), 8 elements per
-// thread per access (LDG.256 for fp32, LDG.128 for 16-bit), one group in flight per thread.
-constexpr int kG = 8, kU = 1, kThreads = 512, kMinBlocks = 2;
-}  // namespace mt
-
 extern "C" int mt_multi_tensor_scale(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float scale,
                                      void* stream_) {
     using namespace mt;
@@ -25,7 +19,7 @@ extern "C" int mt_multi_tensor_scale(int chunk_size, int32_t* noop_flag, const M
         MT_DISPATCH_FHB(tl->dtype[1], Tout, "multi_tensor_scale", {
             using Op = ScaleOp<Tin, Tout>;
             typename Op::Params prm{scale};
-            return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
         }))
     return MT_OK;
 }
@@ -48,7 +42,7 @@ extern "C" int mt_multi_tensor_axpby(int chunk_size, int32_t* noop_flag, const M
             MT_DISPATCH_FHB(tl->dtype[2], To, "multi_tensor_axpby", {
                 using Op = AxpbyOp<Tx, Ty, To>;
                 typename Op::Params prm{a, b, arg_to_check};
-                return launch_persistent<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+                return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
             })))
     return MT_OK;
 }

@@ -2,11 +2,16 @@
 //
 // Replaces the reference's chunk launcher (/root/reference/csrc/multi_tensor_apply.cuh:16-147): instead of
 // packing <=36..110 tensors / <=2560 chunks into a ~14 KB by-value kernel argument and launching repeatedly,
-// one persistent grid walks a DEVICE-RESIDENT tensor table:
+// ONE launch walks a DEVICE-RESIDENT tensor table:
 //
 //   DevTable { ptrs[depth][ntensors], numel[ntensors], tile_begin[ntensors+1] }   (built + cached by mt_table.cu)
 //
-// Work unit = "tile": `tile_elems` consecutive elements of one tensor.  CTA b processes tiles b, b+grid, ...
+// Work unit = "tile": `tile_elems` consecutive elements of one tensor.  The grid is table-driven: CTA b takes tile b
+// (and b+grid, ... when the grid is capped), so the hardware block scheduler is the dynamic tile scheduler.
+// Measured on B200 (profiles/r1_tune_sweep*.log, 28 B/param Adam, 45 GB/step): one 256-thread CTA per 16384-element
+// tile at 4 CTAs/SM streams 6.68 TB/s (= cudaMemcpy D2D on the same box); a resident grid of SMs x occupancy CTAs
+// striding the tiles statically reached only 5.87 TB/s (slow SMs set the finish time), and a cp.async.bulk (TMA)
+// staged ring 6.2 TB/s -- so the streaming kernels use plain 256-bit LDG/STG and many short-lived CTAs.
 // The owning tensor is found with a binary search in tile_begin (uniform across the CTA -> broadcast loads).
 // Inside a tile each thread moves G consecutive elements per access: 32 B (LDG.256/STG.256) for fp32 and 16 B
 // for 16-bit types at G = 8, fully coalesced; a per-tile scalar head/tail peel handles arbitrary element
@@ -383,10 +388,10 @@ __device__ __forceinline__ void fetch_bases(const DevTable& tb, int tensor, char
      ...);
 }
 
-// The persistent kernel.  grid = min(ntiles, SMs * occupancy); static round-robin over tiles.
+// The table-driven kernel.  grid = ntiles (one CTA per tile); the loop only matters when the grid is capped.
 template <class Op, int G, int U, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
-mt_persistent_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __restrict__ noop) {
+mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __restrict__ noop) {
     __shared__ float smem[THREADS / 32];
     if (Op::kEarlyExit) {
         if (*reinterpret_cast<volatile int32_t*>(noop) != 0) return;

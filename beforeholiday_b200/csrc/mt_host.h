@@ -1,5 +1,5 @@
 // mt_host.h -- host-side internals of libmt_b200.so shared by the per-family translation units:
-// error state, device guard, the device-resident table cache and the persistent-grid launcher.
+// error state, device guard, the device-resident table cache and the table-driven launcher.
 #pragma once
 
 #include <atomic>
@@ -48,8 +48,8 @@ int validate_lists(const MtTensorLists* tl, int expect_depth_lo, int expect_dept
 int64_t total_elems(const MtTensorLists* tl);
 
 // ---- tiles ----------------------------------------------------------------------------------------
-// Element-wise ops ignore the caller's chunk_size and pick their own tile: 16384 elements when that still
-// yields enough tiles to balance a persistent grid, shrinking to 4096 for small problems.
+// Element-wise ops ignore the caller's chunk_size and pick their own tile: 16384 elements (8 rounds of a 256-thread
+// CTA) when that still yields several waves of CTAs, shrinking to one round (2048) for small problems.
 int choose_tile_elems(const MtTensorLists* tl, int device);
 uint64_t count_tiles(const MtTensorLists* tl, int tile_elems);
 
@@ -58,30 +58,24 @@ uint64_t count_tiles(const MtTensorLists* tl, int tile_elems);
 int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevTable* out);
 
 // ---- launcher -------------------------------------------------------------------------------------
+// One CTA per tile (see mt_common.cuh for the measurements behind this choice).  gridDim.x can hold 2^31-1 tiles,
+// which get_table() enforces, so the in-kernel tile loop runs once.
 template <class Op, int G, int U, int THREADS, int MINB>
-int launch_persistent(const DevTable& tb, const typename Op::Params& prm, int32_t* noop, int device,
-                      cudaStream_t stream) {
+int launch_table_kernel(const DevTable& tb, const typename Op::Params& prm, int32_t* noop, int device,
+                        cudaStream_t stream) {
+    (void)device;
     if (tb.ntiles == 0) return MT_OK;  // all tensors empty: nothing to do (the reference launches nothing either)
-    auto kernel = mt_persistent_kernel<Op, G, U, THREADS, MINB>;
-    // One occupancy query per (kernel instantiation, device): grid = resident CTAs per SM x SM count.
-    static std::atomic<int> limit_cache[64];
-    if (device < 0 || device >= 64) return set_error(MT_EINVAL, "device ordinal %d out of range", device);
-    int limit = limit_cache[device].load(std::memory_order_relaxed);
-    if (limit == 0) {
-        int occ = 0;
-        MT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, THREADS, 0));
-        DeviceInfo di;
-        int rc = device_info(device, &di);
-        if (rc) return rc;
-        limit = (occ > 0 ? occ : 1) * di.sms;
-        limit_cache[device].store(limit, std::memory_order_relaxed);
-    }
-    const unsigned grid = tb.ntiles < (uint32_t)limit ? tb.ntiles : (unsigned)limit;
-    kernel<<<grid, THREADS, 0, stream>>>(tb, prm, noop);
+    mt_table_kernel<Op, G, U, THREADS, MINB><<<tb.ntiles, THREADS, 0, stream>>>(tb, prm, noop);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     MT_CUDA_OK(cudaGetLastError());
     return MT_OK;
 }
+
+// Launch shape shared by the streaming families: 256 threads, 4 CTAs/SM (<= 64 registers), 8 elements per thread per
+// access (LDG.256 for fp32, LDG.128 for 16-bit), one group in flight per thread; tiles of up to 16384 elements.
+constexpr int kG = 8, kU = 1, kThreads = 256, kMinBlocks = 4;
+constexpr int kRound = kG * kThreads;   // elements one CTA moves per round
+constexpr int kMaxTile = 16384;
 
 // dtype-tag dispatch helpers
 #define MT_CASE(TAG, CT, NAME, ...) \

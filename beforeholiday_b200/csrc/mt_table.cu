@@ -79,11 +79,11 @@ uint64_t count_tiles(const MtTensorLists* tl, int tile_elems) {
 int choose_tile_elems(const MtTensorLists* tl, int device) {
     DeviceInfo di;
     if (device_info(device, &di) != MT_OK || di.sms <= 0) di.sms = 148;
-    // want >= 8 tiles per resident CTA (2 CTAs/SM) so that the static round-robin balances
-    const uint64_t want = (uint64_t)di.sms * 2 * 8;
-    for (int tile = 16384; tile > 4096; tile >>= 1)
+    // want >= 4 waves of (4 CTAs/SM) so that the tail of the last wave is small
+    const uint64_t want = (uint64_t)di.sms * 4 * 4;
+    for (int tile = kMaxTile; tile > kRound; tile >>= 1)
         if (count_tiles(tl, tile) >= want) return tile;
-    return 4096;
+    return kRound;
 }
 
 // ---- table cache --------------------------------------------------------------------------------

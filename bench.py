@@ -320,7 +320,7 @@ def main():
                    "hyper": HP},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": (traffic or {}).get("dram_bytes_per_launch"), "peak_source": peak_src,
-                     "frac_of_8TBps_nominal": achieved / 8000.0, "kernel": "mt_persistent_kernel<DistAdamOp<bf16,copy,noop>>",
+                     "frac_of_8TBps_nominal": achieved / 8000.0, "kernel": "mt_table_kernel<DistAdamOp<bf16,copy,noop>>",
                      "algorithmic_bytes_per_launch": BYTES_PER_PARAM * P},
         "clocks": clocks,
         "gpu_launches": int(launches),

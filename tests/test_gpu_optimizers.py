@@ -105,7 +105,9 @@ def test_fused_adam_multi_device_message():
 def test_fused_sgd_vs_torch(kw, sizes):
     from beforeholiday_b200.optimizers import FusedSGD
 
-    run_pair(lambda ps: torch.optim.SGD(ps, **kw), lambda ps: FusedSGD(ps, **kw), sizes)
+    # atol: torch's CUDA SGD contracts g + wd*p and buf*mu + g into FMAs; the two trajectories differ by rounding
+    # RELATIVE TO THE MOMENTUM BUFFER (|buf| ~ 5-10 x |grad| at momentum 0.9), i.e. ~1e-6 absolute on O(1) params.
+    run_pair(lambda ps: torch.optim.SGD(ps, **kw), lambda ps: FusedSGD(ps, **kw), sizes, atol=2e-6)
 
 
 def test_fused_sgd_half():
