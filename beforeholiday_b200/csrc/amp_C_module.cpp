@@ -19,7 +19,7 @@
 
 namespace {
 
-using TensorLists = std::vector<std::vector<at::Tensor>>;
+using TensorLists = py::object;  // list[list[Tensor]], walked in place (see flatten())
 
 int dtype_tag(at::ScalarType t, const char* who) {
     switch (t) {
@@ -37,35 +37,68 @@ struct Flat {
     std::vector<const void*> ptrs;
     std::vector<int64_t> numel;
     std::vector<at::Tensor> keep;  // densified sparse inputs
+    at::Tensor first;              // tensor_lists[0][0]: device / options for allocations
     c10::DeviceIndex device = 0;
     cudaStream_t stream = nullptr;
 };
 
-// Validation + flattening.  Same checks, same messages as multi_tensor_apply<depth>().
-void flatten(const TensorLists& lists, size_t depth_lo, size_t depth_hi, const char* who, Flat& f) {
-    TORCH_CHECK(lists.size() >= depth_lo && lists.size() <= depth_hi, "tensor_lists.size() != depth");
-    const size_t depth = lists.size();
-    const size_t len0 = lists[0].size();
-    TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
-    auto ref_device = lists[0][0].device();
-    TORCH_CHECK(ref_device.type() == at::kCUDA, "expected input to be on cuda");
-    f.ptrs.resize(depth * len0);
-    f.numel.resize(len0);
+// RAII for PySequence_Fast
+struct FastSeq {
+    PyObject* o;
+    FastSeq(PyObject* src, const char* msg) : o(PySequence_Fast(src, msg)) {
+        if (!o) throw py::error_already_set();
+    }
+    ~FastSeq() { Py_XDECREF(o); }
+    Py_ssize_t size() const { return PySequence_Fast_GET_SIZE(o); }
+    PyObject* operator[](Py_ssize_t i) const { return PySequence_Fast_GET_ITEM(o, i); }
+    FastSeq(const FastSeq&) = delete;
+    FastSeq& operator=(const FastSeq&) = delete;
+};
+
+// Validation + flattening.  Same checks, same messages as multi_tensor_apply<depth>()
+// (/root/reference/csrc/multi_tensor_apply.cuh:53-72), but walking the Python lists directly: the reference's
+// signature (std::vector<std::vector<at::Tensor>> by value) costs a type-cast plus a reference-count round trip per
+// tensor, which at 50k tensors x 3 lists is several milliseconds -- more than the kernel itself on a B200.
+void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, const char* who, Flat& f) {
+    FastSeq outer(lists_obj.ptr(), "tensor_lists must be a sequence of sequences of tensors");
+    const size_t depth = (size_t)outer.size();
+    TORCH_CHECK(depth >= depth_lo && depth <= depth_hi, "tensor_lists.size() != depth");
+    size_t len0 = 0;
+    c10::Device ref_device(c10::kCPU);
     for (size_t l = 0; l < depth; l++) {
-        TORCH_CHECK(lists[l].size() == len0, "Size mismatch among tensor lists");
-        const auto st0 = lists[l][0].scalar_type();
+        FastSeq inner(outer[l], "tensor_lists must be a sequence of sequences of tensors");
+        const size_t len = (size_t)inner.size();
+        if (l == 0) {
+            len0 = len;
+            TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
+            TORCH_CHECK(THPVariable_Check(inner[0]), who, ": tensor_lists must contain tensors");
+            f.first = THPVariable_Unpack(inner[0]);
+            ref_device = f.first.device();
+            TORCH_CHECK(ref_device.type() == at::kCUDA, "expected input to be on cuda");
+            f.ptrs.resize(depth * len0);
+            f.numel.resize(len0);
+        }
+        TORCH_CHECK(len == len0, "Size mismatch among tensor lists");
+        at::ScalarType st0 = at::ScalarType::Undefined;
         for (size_t t = 0; t < len0; t++) {
-            const at::Tensor& x = lists[l][t];
-            bool contiguous_memory = x.is_sparse() ? x._values().is_contiguous() : x.is_contiguous();
-            contiguous_memory = contiguous_memory || x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
-                                x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
+            PyObject* item = inner[t];
+            TORCH_CHECK(THPVariable_Check(item), who, ": tensor_lists must contain tensors");
+            const at::Tensor& x = THPVariable_Unpack(item);
+            const bool sparse = x.is_sparse();
+            bool contiguous_memory = sparse ? x._values().is_contiguous() : x.is_contiguous();
+            if (!contiguous_memory)
+                contiguous_memory = x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
+                                    x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
             TORCH_CHECK(contiguous_memory, "A tensor was not contiguous.");
             TORCH_CHECK(x.device() == ref_device, "A tensor was not on the same device as the first tensor");
-            TORCH_CHECK(x.numel() == lists[0][t].numel(), "Size mismatch");
+            const int64_t n = x.numel();
+            if (l == 0) f.numel[t] = n;
+            else TORCH_CHECK(n == f.numel[t], "Size mismatch");
             // The reference dispatches on element [0] of each list and reinterprets the rest; a mixed list is a
             // silent misread there.  Here it is an error.
-            TORCH_CHECK(x.scalar_type() == st0, who, ": all tensors of one list must share a dtype");
-            if (x.is_sparse()) {  // densify, as multi_tensor_apply.cuh:92-95
+            if (t == 0) st0 = x.scalar_type();
+            else TORCH_CHECK(x.scalar_type() == st0, who, ": all tensors of one list must share a dtype");
+            if (sparse) {  // densify, as multi_tensor_apply.cuh:92-95
                 at::Tensor dst = at::zeros(x.sizes(), x.options().layout(at::kStrided));
                 dst.add_(x);
                 f.keep.push_back(dst);
@@ -73,7 +106,6 @@ void flatten(const TensorLists& lists, size_t depth_lo, size_t depth_hi, const c
             } else {
                 f.ptrs[l * len0 + t] = x.data_ptr();
             }
-            if (l == 0) f.numel[t] = x.numel();
         }
         f.tl.dtype[l] = dtype_tag(st0, who);
     }
@@ -108,13 +140,13 @@ void multi_tensor_axpby(int chunk_size, at::Tensor noop_flag, TensorLists tensor
     check(mt_multi_tensor_axpby(chunk_size, flag_ptr(noop_flag), &f.tl, a, b, arg_to_check, f.stream));
 }
 
-std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_flag, const TensorLists& tensor_lists,
+std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_flag, const py::object& tensor_lists,
                                                bool with_scale, float scale, at::optional<bool> per_tensor_python) {
     const bool per_tensor = per_tensor_python.has_value() ? per_tensor_python.value() : false;
     Flat f;
     flatten(tensor_lists, with_scale ? 2 : 1, with_scale ? 2 : 1, with_scale ? "multi_tensor_l2norm_scale" : "multi_tensor_l2norm", f);
     const c10::cuda::CUDAGuard guard(f.device);
-    auto fopt = tensor_lists[0][0].options().dtype(at::kFloat).layout(at::kStrided);
+    auto fopt = f.first.options().dtype(at::kFloat).layout(at::kStrided);
     at::Tensor ret = at::empty({1}, fopt);
     at::Tensor ret_per_tensor = at::empty({per_tensor ? (int64_t)f.tl.ntensors : 0}, fopt);
     const size_t sbytes = mt_norm_scratch_bytes(chunk_size, &f.tl);
@@ -156,10 +188,8 @@ void multi_tensor_sgd(int chunk_size, at::Tensor noop_flag, TensorLists tensor_l
                       float dampening, float lr, bool nesterov, bool first_run, bool wd_after_momentum, float scale) {
     Flat f;
     flatten(tensor_lists, 3, 4, "multi_tensor_sgd", f);
-    if (tensor_lists.size() == 4)
-        for (const auto& t : tensor_lists[3])
-            TORCH_CHECK(t.scalar_type() == at::ScalarType::Half, "Additional output tensors should always be fp16.");
-    TORCH_CHECK(noop_flag.device() == tensor_lists[0][0].device(),
+    if (f.tl.depth == 4) TORCH_CHECK(f.tl.dtype[3] == MT_F16, "Additional output tensors should always be fp16.");
+    TORCH_CHECK(noop_flag.device() == f.first.device(),
                 "expected noop flag to be on the same device as tensors");
     check(mt_multi_tensor_sgd(chunk_size, flag_ptr(noop_flag), &f.tl, wd, momentum, dampening, lr, nesterov, first_run,
                               wd_after_momentum, scale, f.stream));
@@ -177,7 +207,7 @@ void multi_tensor_lamb(int chunk_size, at::Tensor noop_flag, TensorLists tensor_
     const c10::cuda::CUDAGuard guard(f.device);
     const size_t sbytes = mt_lamb_scratch_bytes(chunk_size, &f.tl);
     at::Tensor scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)},
-                                   tensor_lists[0][0].options().dtype(at::kByte).layout(at::kStrided));
+                                   f.first.options().dtype(at::kByte).layout(at::kStrided));
     check(mt_multi_tensor_lamb(chunk_size, flag_ptr(noop_flag), &f.tl, lr, beta1, beta2, epsilon, step, bias_correction,
                                weight_decay, grad_averaging, mode, global_grad_norm.data_ptr<float>(), max_grad_norm,
                                use_nvlamb, scratch.data_ptr(), sbytes, f.stream));
@@ -215,7 +245,7 @@ void multi_tensor_fused_adam(int chunk_size, at::Tensor noop_flag, TensorLists t
                              at::Tensor per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
                              bool honour_noop) {
     Flat f;
-    TORCH_CHECK(tensor_lists.size() == 4 || tensor_lists.size() == 5, "expected tensor lists of size 4 or 5");
+    TORCH_CHECK(py::len(tensor_lists) == 4 || py::len(tensor_lists) == 5, "expected tensor lists of size 4 or 5");
     flatten(tensor_lists, 4, 5, "multi_tensor_fused_adam", f);
     const int64_t n = f.tl.ntensors;
     TORCH_CHECK(per_tensor_beta1.numel() >= n && per_tensor_beta2.numel() >= n && per_tensor_bias_correction.numel() >= n &&

@@ -6,7 +6,7 @@
 One JSON line on stdout (rank 0).  A "step" is one optimizer step over one synthetic parameter set:
 
   N = 1   Llama-3-8B parameter set (8 030 261 248 params, 291 tensors), mixed-precision AdamW: bf16 grads, fp32
-          master p / m / v, bf16 model copy = 28 algorithmic bytes per parameter, ONE persistent-grid launch through
+          master p / m / v, bf16 model copy = 28 algorithmic bytes per parameter, ONE table-driven launch through
           the public op `amp_C.multi_tensor_fused_adam` (the reference's 28 B/param interface,
           apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp:3-19).
   N > 1   the same parameter set with the optimizer state sharded ZeRO-2 style over N ranks
@@ -319,7 +319,11 @@ def main():
                    "bytes_per_param": BYTES_PER_PARAM, "l2": "inputs (16 B/param resident) are >> L2; no flush needed",
                    "hyper": HP},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": (traffic or {}).get("dram_bytes_per_launch"), "peak_source": peak_src,
+                     "traffic": (BYTES_PER_PARAM * P * traffic["traffic_over_algorithmic"]) if traffic else None,
+                     "traffic_source": (f"ncu dram bytes / algorithmic bytes = {traffic['traffic_over_algorithmic']} measured on "
+                                        f"{traffic['captured_workload']} ({traffic['source']}), scaled to this launch")
+                     if traffic else None,
+                     "peak_source": peak_src,
                      "frac_of_8TBps_nominal": achieved / 8000.0, "kernel": "mt_table_kernel<DistAdamOp<bf16,copy,noop>>",
                      "algorithmic_bytes_per_launch": BYTES_PER_PARAM * P},
         "clocks": clocks,

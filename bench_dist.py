@@ -1,0 +1,134 @@
+"""bench_dist.py -- the N > 1 leg of bench.py: ZeRO-2 sharded mixed-precision AdamW over N B200s of one node.
+
+Step (timed, all of it): reduce-scatter of the bf16 gradients -> update of this rank's 1/N shard (fp32 p/m/v) ->
+all-gather of the updated bf16 parameters.  Total work is fixed (strong scaling); `value` = params of the WHOLE set /
+max-over-ranks step time.  The line also breaks the step down (update kernel only, reduce-scatter only, all-gather only)
+because the end-to-end step is NVLink-bound: 2 B/param must leave and enter every GPU twice.
+"""
+from __future__ import annotations
+
+import json
+import sys
+import time
+
+import torch
+import torch.distributed as dist
+
+import workloads
+from bench import BYTES_PER_PARAM, HP, METRIC, UNIT, ClockSampler, log, peaks
+
+
+def _timed(fn, steps, device):
+    dist.barrier()
+    torch.cuda.synchronize(device)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.time()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize(device)
+    dist.barrier()
+    t1 = time.time()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], device=device)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), t0, t1
+
+
+def run_distributed(args, rank, world, local_rank, device):
+    import beforeholiday_b200
+    from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+
+    amp_C = beforeholiday_b200.load_amp_C()
+    shapes = workloads.WORKLOADS[args.workload]()
+    numels = workloads.numels(shapes)
+    P = sum(numels)
+    opt = DistributedFusedAdam(numels=numels, lr=HP["lr"], betas=(HP["beta1"], HP["beta2"]), eps=HP["eps"],
+                               weight_decay=HP["wd"], adam_w_mode=True, device=device, bucket_cap_mb=1024.0,
+                               grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16)
+    L = opt.layout
+    if rank == 0:
+        log(f"[bench] {args.workload}: {len(numels)} tensors, {P} params; world={world}, {L.nbuckets} buckets of "
+            f"{L.bucket_elems} elems, shard {L.state_elems} elems/rank, {len(opt.frags)} fragments on rank 0")
+    CH = 1 << 28
+    gen = torch.Generator(device=device).manual_seed(1234)          # same params on every rank
+    for o in range(0, L.padded, CH):
+        opt.params_flat[o:o + CH].normal_(0, 0.02, generator=gen)
+    opt.init_master_from_params()
+    gen = torch.Generator(device=device).manual_seed(100 + rank)     # each rank's own gradients
+    for o in range(0, L.padded, CH):
+        opt.grads_flat[o:o + CH].normal_(0, 1e-3, generator=gen)
+    torch.cuda.synchronize(device)
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    for _ in range(args.warmup):
+        opt.step()
+    launches0 = amp_C.launch_count()
+    ms, t0, t1 = _timed(opt.step, args.steps, device)
+    launches = amp_C.launch_count() - launches0
+    clocks = ClockSampler.summarize(sampler.window(t0, t1)) if sampler else None
+
+    # breakdown (each max over ranks)
+    ms_update, _, _ = _timed(lambda: [opt._update_bucket(b, float(world)) for b in range(L.nbuckets)], args.steps, device)
+    ms_rs, _, _ = _timed(lambda: [opt._reduce_scatter(b) for b in range(L.nbuckets)], max(2, args.steps // 2), device)
+    ms_ag, _, _ = _timed(lambda: [opt._all_gather(b) for b in range(L.nbuckets)], max(2, args.steps // 2), device)
+    rs_s, ag_s = opt.rs_stream, opt.ag_stream
+    opt.rs_stream = None
+    ms_serial, _, _ = _timed(opt.step, max(2, args.steps // 2), device)
+    opt.rs_stream, opt.ag_stream = rs_s, ag_s
+
+    # e2e: every rank's gradients arrive from pinned host memory each step (H2D inside the timed region), the step's
+    # skip flag is read back (D2H).  PCIe-bound: 2 B/param per rank per step.
+    e2e = None
+    if not args.no_e2e:
+        win = min(L.padded, 1 << 30)                       # 2 GiB pinned window per rank, cycled over the flat space
+        host = torch.empty(win, dtype=torch.bfloat16, pin_memory=True)
+        host.copy_(opt.grads_flat[:win])
+        host_flag = torch.zeros(1, dtype=torch.int32, pin_memory=True)
+
+        def e2e_step():
+            for o in range(0, L.padded, win):
+                n = min(win, L.padded - o)
+                opt.grads_flat[o:o + n].copy_(host[:n], non_blocking=True)
+            opt.step()
+            host_flag.copy_(opt.noop, non_blocking=True)
+            torch.cuda.current_stream(device).synchronize()
+
+        e2e_step()
+        ms_e2e, _, _ = _timed(e2e_step, max(2, min(args.steps, 3)), device)
+        e2e = {"value": P / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * L.padded * world,
+               "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e,
+               "note": "each rank copies its full bf16 gradient buffer from pinned host memory every step, then "
+                       "reduce-scatter -> update -> all-gather; the skip flag is read back; bytes are summed over ranks"}
+    if sampler:
+        sampler.stop()
+    if rank == 0:
+        peak, peak_src = peaks()
+        shard_bytes = BYTES_PER_PARAM * L.state_elems
+        achieved = shard_bytes / (ms_update * 1e-3) / 1e9
+        nvlink_bytes = 2 * L.padded * (world - 1) / world  # bytes each GPU sends (and receives) per collective
+        line = {
+            "metric": METRIC, "value": P / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload}: ZeRO-2 sharded mixed-precision AdamW ({P} params, {len(numels)} tensors): "
+                                   f"reduce-scatter bf16 grads -> shard update (fp32 p/m/v) -> all-gather bf16 params",
+                       "parallelism": f"optimizer state sharded x{world}, {L.nbuckets} buckets pipelined on 3 streams",
+                       "bytes_per_param": BYTES_PER_PARAM, "l2": "inputs >> L2; no flush needed", "hyper": HP},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "mt_table_kernel<DistAdamOp<bf16,copy,noop>> (shard update only)",
+                         "algorithmic_bytes_per_launch": shard_bytes / max(1, L.nbuckets)},
+            "breakdown_ms": {"step_overlapped": ms, "step_serial": ms_serial, "update_only": ms_update,
+                             "reduce_scatter_only": ms_rs, "all_gather_only": ms_ag},
+            "update_only": {"params_per_s_whole_job": P / (ms_update * 1e-3), "hbm_gbs_per_gpu": achieved},
+            "nvlink": {"bytes_sent_per_gpu_per_collective": nvlink_bytes,
+                       "reduce_scatter_GBps_per_gpu": nvlink_bytes / (ms_rs * 1e-3) / 1e9,
+                       "all_gather_GBps_per_gpu": nvlink_bytes / (ms_ag * 1e-3) / 1e9},
+            "clocks": clocks, "gpu_launches": int(launches),
+            "e2e": e2e if e2e is not None else {"value": None, "unit": UNIT, "h2d_bytes_per_step": None,
+                                                "d2h_bytes_per_step": None, "note": "skipped (--no-e2e)"},
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    return 0

@@ -1,0 +1,93 @@
+"""2-GPU test of the sharded optimizer over NCCL (skipped on a 1-GPU box; run with `gpurun --gpus 2`):
+the gathered bf16 parameters after 3 sharded steps must equal, bit for bit, the CPU oracle's single-process result on
+the summed gradients (reduce-scatter sums are computed by NCCL in bf16: tested with exactly representable inputs)."""
+import os
+import socket
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [1000, 7, 4096, 33333, 1, 129, 300001]
+
+
+def _worker(rank, world, port, outdir):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+
+        wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
+        opt = DistributedFusedAdam(numels=SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, device=f"cuda:{rank}",
+                                   bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds)
+        L = opt.layout
+        assert L.nbuckets > 1
+        torch.manual_seed(0)
+        for n, o in zip(SIZES, L.offsets):
+            opt.params_flat[o:o + n].copy_(torch.randn(n) * 0.02)
+        opt.init_master_from_params()
+        for it in range(3):
+            opt.zero_grad()
+            g = torch.Generator().manual_seed(100 * it + rank)
+            for n, o in zip(SIZES, L.offsets):
+                # multiples of 2^-10 in [-4, 4): sums of two are exact in bf16
+                opt.grads_flat[o:o + n].copy_((torch.randint(-64, 64, (n,), generator=g).float() / 1024))
+            opt.step()
+        gn = opt.grad_norm()
+        torch.cuda.synchronize()
+        out = [opt.params_flat[o:o + n].cpu().clone() for n, o in zip(SIZES, L.offsets)]
+        torch.save({"params": out, "noop": int(opt.noop.item()), "gn": float(gn.item())}, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.timeout(600)
+def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+
+    world = 2
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(500)
+        assert p.exitcode == 0
+    res = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
+    for a, b in zip(res[0]["params"], res[1]["params"]):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    assert res[0]["noop"] == 0 and abs(res[0]["gn"] - res[1]["gn"]) <= 1e-6 * res[0]["gn"]
+
+    torch.manual_seed(0)
+    p32 = [(torch.randn(n) * 0.02).bfloat16().float() for n in SIZES]
+    m = [torch.zeros(n) for n in SIZES]
+    v = [torch.zeros(n) for n in SIZES]
+    pc = [torch.zeros(n, dtype=torch.bfloat16) for n in SIZES]
+    wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
+    k = len(SIZES)
+    for it in range(3):
+        gs = [torch.zeros(n) for n in SIZES]
+        for r in range(world):
+            g = torch.Generator().manual_seed(100 * it + r)
+            for i, n in enumerate(SIZES):
+                gs[i] += torch.randint(-64, 64, (n,), generator=g).float() / 1024
+        gs = [x.bfloat16() for x in gs]
+        oracle.multi_tensor_fused_adam(8192, torch.zeros(1, dtype=torch.int32), [p32, m, v, gs, pc], [0.9] * k, [0.95] * k,
+                                       [1] * k, [1e-8] * k, wds, 1e-2, float(world), it + 1, 1)
+    for a, b in zip(res[0]["params"], pc):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))

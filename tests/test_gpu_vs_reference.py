@@ -66,7 +66,17 @@ def check_close(a, b, what):
         # atol: an absolute floor for values that are differences of larger quantities (cancellation)
         assert rel_close(a, b, 1e-6, 1e-7 * float(b.abs().max().clamp_min(1e-30))), f"{what}: max rel {max_rel(a, b)}"
     else:
-        assert ulp_diff_16(a, b) <= 1, f"{what}: {ulp_diff_16(a, b)} ulp"
+        # 16-bit outputs: within 1 ulp.  Where the fp32 value being rounded is itself a near-total cancellation (e.g.
+        # beta1*m + (1-beta1)*g with opposite signs) its fp32 rounding error -- FMA vs separate multiply/add -- can span
+        # several ulps of the tiny 16-bit result; those elements are held to an absolute bound of 2^-20 of the tensor's
+        # largest magnitude instead (4 fp32 ulps of the operands).
+        af, bf_ = a.float().cpu(), b.float().cpu()
+        ia = a.cpu().view(torch.int16).to(torch.int32)
+        ib = b.cpu().view(torch.int16).to(torch.int32)
+        key = lambda i: torch.where(i < 0, -(i & 0x7fff), i)
+        ulp = (key(ia) - key(ib)).abs()
+        ok = (ulp <= 1) | ((af - bf_).abs() <= float(bf_.abs().max()) * 2.0 ** -20) | (af.isnan() & bf_.isnan())
+        assert bool(ok.all()), f"{what}: {int((~ok).sum())} elements beyond 1 ulp, worst {int(ulp[~ok].max())} ulp"
 
 
 @pytest.mark.parametrize("in_t,out_t", [(F16, F32), (F32, F16), (F32, F32), (BF16, F32), (F32, BF16)])
@@ -141,7 +151,9 @@ def test_adam_vs_reference(amp_C, ref_amp_C, oracle, dt, mode, wd):
     lists[3] = [t.abs() for t in lists[3]]
     l1, l2, lo = clone(lists), clone(lists), cpu_clone(lists)
     args = (5e-4, 0.9, 0.999, 1e-8, 5, mode, 1, wd)
-    for _ in range(3):  # a few steps so m / v are not trivially zero-initialised
+    # fp32: a few steps.  16-bit state: one step -- a 1-ulp difference stored in 16-bit m / v legitimately feeds back
+    # into later steps, so only the single-step result can be held to 1 ulp.
+    for _ in range(3 if dt == F32 else 1):
         amp_C.multi_tensor_adam(8192, flag(), l1, *args)
         ref_amp_C.multi_tensor_adam(8192, flag(), l2, *args)
         oracle.multi_tensor_adam(8192, torch.zeros(1, dtype=torch.int32), lo, *args)
