@@ -138,6 +138,28 @@ int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTenso
                                const float* per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
                                int honour_noop, void* stream);
 
+/* L2 norm for callers that cannot allocate.  No counterpart in the reference (its multi_tensor_l2norm_cuda allocates
+ * four tensors per call through torch).
+ *
+ * Same result as mt_multi_tensor_l2norm (same kernels, same summation order), but it takes no scratch pointer and makes
+ * no cudaMalloc / cudaFree / cudaMallocHost call of its own: the tensor table and the per-chunk partial sums live in a
+ * fixed __device__ array inside the library, mt_noalloc_resident_bytes() bytes (about 1.3 MB) on every GPU that loads it.
+ * Meant for hosts bound to the bare C ABI that own no device allocator, for processes that gave all of HBM to one pool
+ * at start-up (cudaMalloc would fail), and for steps that must not incur cudaMalloc's device-wide synchronisation.
+ *
+ * Limits: at most MT_NOALLOC_MAX_TENSORS tensors and MT_NOALLOC_MAX_CHUNKS chunks (sum over tensors of
+ * ceil(numel / chunk_size)); beyond either the call returns MT_EINVAL with a message and launches nothing.
+ * The array is shared by all calls in the process and is never cleared (nothing in it needs to start at zero: a call
+ * reads only what it has itself just written).  Calls whose GPU work overlaps -- different streams or threads -- race
+ * on it; calls on one stream are safe.  The first call on each device resolves the array's address
+ * (cudaGetSymbolAddress): issue it before any stream capture begins.  The table is uploaded from pageable host
+ * memory, so the call may wait for earlier work on `stream`. */
+#define MT_NOALLOC_MAX_TENSORS 16384
+#define MT_NOALLOC_MAX_CHUNKS 262144
+int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
+                                   float* ret, float* ret_per_tensor, void* stream);
+size_t mt_noalloc_resident_bytes(void);
+
 /* Device-table cache introspection (the table replaces the by-value TensorListMetadata kernel argument,
  * /root/reference/csrc/multi_tensor_apply.cuh:19-26). */
 typedef struct MtCacheStats {
