@@ -17,7 +17,7 @@ EXPORTS = [
     "mt_last_error", "mt_version", "mt_multi_tensor_scale", "mt_multi_tensor_axpby", "mt_norm_scratch_bytes",
     "mt_lamb_scratch_bytes", "mt_multi_tensor_l2norm", "mt_multi_tensor_l2norm_scale", "mt_multi_tensor_adam",
     "mt_multi_tensor_sgd", "mt_multi_tensor_lamb", "mt_multi_tensor_lamb_stage1", "mt_multi_tensor_lamb_stage2",
-    "mt_multi_tensor_fused_adam", "mt_multi_tensor_l2norm_noalloc", "mt_noalloc_resident_bytes",
+    "mt_multi_tensor_fused_adam", "mt_multi_tensor_fused_adam_p2p", "mt_multi_tensor_l2norm_noalloc", "mt_noalloc_resident_bytes",
     "mt_table_cache_stats", "mt_table_cache_clear", "mt_launch_count",
 ]
 

@@ -14,6 +14,9 @@ shard update + param all-gather :977-1115) re-laid-out for one NVSwitch node:
                          g / grad_scale fused) -> all_gather(params, in place)
                          The three stages of successive buckets run on three streams (two NCCL communicators), so the
                          update and the two collectives overlap; NVLink carries both directions at once.
+  step_fused()           (fused_p2p=True) ONE kernel does all three: it sums the gradient shard straight out of every
+                         peer's buffer and stores the updated parameters straight into every peer's buffer
+                         (amp_C.multi_tensor_fused_adam_p2p over symmetric memory), a barrier on each side.
   grad norm / clipping   local sum of squares over the owned fragments (amp_C.multi_tensor_l2norm) -> scalar
                          all_reduce(SUM) -> sqrt (reference :808-887); the overflow flag is all_reduce(MAX)-ed.
 
@@ -101,7 +104,8 @@ class DistributedFusedAdam:
     def __init__(self, params=None, numels: Optional[Sequence[int]] = None, lr=1e-3, bias_correction=True,
                  betas=(0.9, 0.999), eps=1e-8, adam_w_mode=True, weight_decay=0.0, grad_dtype=torch.bfloat16,
                  param_dtype=torch.bfloat16, process_group=None, device=None, bucket_cap_mb: float = 1024.0,
-                 average_grad_sync=True, overlap=True, per_param_weight_decay: Optional[Sequence[float]] = None):
+                 average_grad_sync=True, overlap=True, per_param_weight_decay: Optional[Sequence[float]] = None,
+                 fused_p2p: bool = False):
         assert (params is None) != (numels is None), "give exactly one of params / numels"
         self.group = process_group
         self.world = dist.get_world_size(self.group) if dist.is_initialized() else 1
@@ -119,6 +123,7 @@ class DistributedFusedAdam:
         self.bias_correction, self.adam_w_mode, self.weight_decay = bias_correction, adam_w_mode, weight_decay
         self.average_grad_sync = average_grad_sync
         self.overlap = overlap
+        self.fused_p2p = bool(fused_p2p) and self.world > 1
         self.step_count = 0
         esz = torch.empty((), dtype=grad_dtype).element_size()
         self.layout = FlatLayout(numels, self.world, self.rank, esz, int(bucket_cap_mb * 1024 * 1024 / esz))
@@ -134,8 +139,30 @@ class DistributedFusedAdam:
     # ---- buffers ---------------------------------------------------------------------------------------------------
     def _alloc(self):
         L = self.layout
-        self.grads_flat = torch.zeros(L.padded, dtype=self.grad_dtype, device=self.device)
-        self.params_flat = torch.zeros(L.padded, dtype=self.param_dtype, device=self.device)
+        if self.fused_p2p:
+            # Symmetric allocations: every rank maps every other rank's buffers, so the update kernel can read the
+            # gradient shard from, and write the updated parameters to, all peers directly over NVLink.
+            import torch.distributed._symmetric_memory as symm_mem
+
+            assert self.grad_dtype == self.param_dtype, "fused_p2p needs one 16-bit dtype for gradients and parameters"
+            grp = dist.group.WORLD if self.group is None else self.group
+            self.grads_flat = symm_mem.empty(L.padded, dtype=self.grad_dtype, device=self.device)
+            self.params_flat = symm_mem.empty(L.padded, dtype=self.param_dtype, device=self.device)
+            self.grads_flat.zero_()
+            self.params_flat.zero_()
+            self._hdl_g = symm_mem.rendezvous(self.grads_flat, group=grp)
+            self._hdl_p = symm_mem.rendezvous(self.params_flat, group=grp)
+            self._grad_ptrs = [int(x) for x in self._hdl_g.buffer_ptrs]
+            self._param_ptrs = [int(x) for x in self._hdl_p.buffer_ptrs]
+            # NVSwitch multicast addresses (0 when the fabric has no NVLS): in-switch reduction and broadcast
+            self._grad_mc = int(getattr(self._hdl_g, "multicast_ptr", 0) or 0)
+            self._param_mc = int(getattr(self._hdl_p, "multicast_ptr", 0) or 0)
+            self.has_multicast = self._grad_mc != 0 and self._param_mc != 0
+            assert self._grad_ptrs[self.rank] == self.grads_flat.data_ptr()
+            assert self._param_ptrs[self.rank] == self.params_flat.data_ptr()
+        else:
+            self.grads_flat = torch.zeros(L.padded, dtype=self.grad_dtype, device=self.device)
+            self.params_flat = torch.zeros(L.padded, dtype=self.param_dtype, device=self.device)
         self.p32 = torch.zeros(L.state_elems, dtype=torch.float32, device=self.device)
         self.m = torch.zeros(L.state_elems, dtype=torch.float32, device=self.device)
         self.v = torch.zeros(L.state_elems, dtype=torch.float32, device=self.device)
@@ -227,6 +254,38 @@ class DistributedFusedAdam:
             return
         self._amp_C().multi_tensor_fused_adam(8192, self.noop, lists, *hp, self.lr, grad_scale, self.step_count,
                                               1 if self.adam_w_mode else 0, True)
+
+    def _all_fragments_launch_set(self, wd_of=None):
+        if getattr(self, "_all_set", None) is None:
+            lists = [[], [], [], [], []]
+            hps = [[], [], [], [], []]
+            for (bl, hp) in self._per_bucket:
+                if not bl[0]:
+                    continue
+                for d in range(5):
+                    lists[d] += bl[d]
+                    hps[d].append(hp[d])
+            self._all_set = (lists, tuple(torch.cat(h) for h in hps))
+        return self._all_set
+
+    def step_fused(self, grad_scale: float = 1.0, multicast: Optional[bool] = None):
+        """One step with BOTH collectives folded into the update kernel (amp_C.multi_tensor_fused_adam_p2p): each rank
+        reads its gradient shard from every peer's buffer and writes its updated parameters into every peer's buffer.
+        A cross-GPU barrier on each side makes the peers' gradients complete before and the parameter writes visible
+        after (symmetric-memory signal pads; stream-ordered, no host sync).  With NVSwitch multicast available
+        (`has_multicast`) the sum and the broadcast happen inside the switch (multimem.ld_reduce / multimem.st)."""
+        assert self.fused_p2p, "construct with fused_p2p=True"
+        self.step_count += 1
+        scale = grad_scale * (self.world if self.average_grad_sync else 1)
+        lists, hp = self._all_fragments_launch_set()
+        use_mc = self.has_multicast if multicast is None else (bool(multicast) and self.has_multicast)
+        self._hdl_g.barrier(channel=0)
+        if lists[0]:
+            self._amp_C().multi_tensor_fused_adam_p2p(8192, self.noop, lists, *hp, self.lr, scale, self.step_count,
+                                                      1 if self.adam_w_mode else 0, self.rank, self._grad_ptrs,
+                                                      self._param_ptrs, self._grad_mc if use_mc else 0,
+                                                      self._param_mc if use_mc else 0)
+        self._hdl_p.barrier(channel=1)
 
     def grad_norm(self, grads_are_reduced: bool = True) -> torch.Tensor:
         """Global L2 norm of the (reduced) gradients: local shard sum of squares -> all_reduce(SUM) -> sqrt.

@@ -258,6 +258,33 @@ void multi_tensor_fused_adam(int chunk_size, at::Tensor noop_flag, TensorLists t
                                      grad_scale, step, mode, honour_noop ? 1 : 0, f.stream));
 }
 
+// Fused reduce-scatter + Adam + all-gather over peer memory.  grad_ptrs / param_ptrs: every rank's flat buffer base
+// address as mapped in this process (e.g. torch.distributed._symmetric_memory handle.buffer_ptrs).
+void multi_tensor_fused_adam_p2p(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                 at::Tensor per_tensor_beta1, at::Tensor per_tensor_beta2,
+                                 at::Tensor per_tensor_bias_correction, at::Tensor per_tensor_eps,
+                                 at::Tensor per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
+                                 int rank, std::vector<uint64_t> grad_ptrs, std::vector<uint64_t> param_ptrs,
+                                 uint64_t grad_multicast_ptr, uint64_t param_multicast_ptr) {
+    Flat f;
+    flatten(tensor_lists, 5, 5, "multi_tensor_fused_adam_p2p", f);
+    TORCH_CHECK(grad_ptrs.size() == param_ptrs.size(), "grad_ptrs and param_ptrs must have one entry per rank");
+    const int world = (int)grad_ptrs.size();
+    std::vector<const void*> gb(world);
+    std::vector<void*> pb(world);
+    for (int r = 0; r < world; r++) {
+        gb[r] = reinterpret_cast<const void*>(grad_ptrs[r]);
+        pb[r] = reinterpret_cast<void*>(param_ptrs[r]);
+    }
+    TORCH_CHECK(per_tensor_bias_correction.scalar_type() == at::ScalarType::Int, "per_tensor_bias_correction must be int32");
+    check(mt_multi_tensor_fused_adam_p2p(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(),
+                                         per_tensor_beta2.data_ptr<float>(), per_tensor_bias_correction.data_ptr<int32_t>(),
+                                         per_tensor_eps.data_ptr<float>(), per_tensor_weight_decay.data_ptr<float>(), lr,
+                                         grad_scale, step, mode, world, rank, gb.data(), pb.data(),
+                                         reinterpret_cast<const void*>(grad_multicast_ptr),
+                                         reinterpret_cast<void*>(param_multicast_ptr), f.stream));
+}
+
 py::dict table_cache_stats(int device) {
     MtCacheStats s{};
     check(mt_table_cache_stats(device, &s));
@@ -290,6 +317,13 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),
           py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
           py::arg("honour_noop") = false);
+    m.def("multi_tensor_fused_adam_p2p", &multi_tensor_fused_adam_p2p,
+          "Fused gradient reduce-scatter + sharded Adam + parameter all-gather over NVLink peer memory",
+          py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor_beta1"),
+          py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),
+          py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
+          py::arg("rank"), py::arg("grad_ptrs"), py::arg("param_ptrs"), py::arg("grad_multicast_ptr") = 0,
+          py::arg("param_multicast_ptr") = 0);
     m.def("launch_count", []() { return mt_launch_count(); }, "kernels launched by libmt_b200.so since load");
     m.def("table_cache_stats", &table_cache_stats, "device tensor-table cache counters");
     m.def("table_cache_clear", [](int device) { check(mt_table_cache_clear(device)); });

@@ -1,0 +1,82 @@
+// mt_api_p2p.cu -- mt_multi_tensor_fused_adam_p2p: gradient reduce-scatter + sharded Adam + parameter all-gather in ONE
+// kernel over NVLink peer memory, for the ZeRO-style step of SURVEY.md section 8(e).
+//
+// The NCCL route (reduce_scatter -> update -> all_gather, distributed_fused_adam.py in the reference, :668-742 and
+// :977-1115) moves every gradient byte over NVLink into a local buffer, reads it back from HBM in the update, writes
+// the updated parameters to HBM and reads them again to send them.  Here the update kernel itself loads the gradient
+// shard straight from every peer (ld.global on peer-mapped addresses, summed in rank order) and stores the updated
+// 16-bit parameters straight into every peer's buffer, tile by tile, so the link transfers overlap the HBM traffic of
+// p / m / v and nothing is staged.  The caller provides the peer-mapped base addresses (symmetric allocations, e.g.
+// torch.distributed._symmetric_memory) and a cross-GPU barrier before and after the launch.
+#include <cstring>
+
+#include "mt_host.h"
+#include "mt_ops.cuh"
+
+namespace mt {
+
+template <class Tg, int WORLD, bool kMc, int MINB>
+static int launch_p2p(const DevTable& tb, const typename DistAdamOp<Tg, true, true>::Params& base, int rank,
+                      const void* const* grad_bases, void* const* param_bases, const void* grad_mc, void* param_mc,
+                      int32_t* noop, int device, cudaStream_t stream) {
+    using Op = DistAdamP2POp<Tg, WORLD, kMc>;
+    typename Op::Params prm;
+    prm.base = base;
+    prm.gown = static_cast<const char*>(grad_bases[rank]);
+    prm.pown = static_cast<char*>(param_bases[rank]);
+    prm.gmc = static_cast<const char*>(grad_mc);
+    prm.pmc = static_cast<char*>(param_mc);
+    for (int r = 0; r < WORLD; r++) {
+        prm.gbase[r] = static_cast<const char*>(grad_bases[r]);
+        prm.pbase[r] = static_cast<char*>(param_bases[r]);
+    }
+    return launch_table_kernel<Op, kG, kU, kThreads, MINB>(tb, prm, noop, device, stream);
+}
+
+}  // namespace mt
+
+extern "C" int mt_multi_tensor_fused_adam_p2p(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                              const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                              const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                              const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                                              int mode, int world, int rank, const void* const* grad_bases,
+                                              void* const* param_bases, const void* grad_multicast,
+                                              void* param_multicast, void* stream_) {
+    using namespace mt;
+    (void)chunk_size;
+    const char* who = "multi_tensor_fused_adam_p2p";
+    int rc = validate_lists(tl, 5, 5, who);
+    if (rc) return rc;
+    if (!noop_flag) return set_error(MT_EINVAL, "%s: noop_flag is NULL", who);
+    if (!per_tensor_beta1 || !per_tensor_beta2 || !per_tensor_bias_correction || !per_tensor_eps || !per_tensor_weight_decay)
+        return set_error(MT_EINVAL, "%s: per-tensor hyper-parameter arrays must be device pointers", who);
+    if (world != 2 && world != 4 && world != 8) return set_error(MT_EINVAL, "%s: world must be 2, 4 or 8 (got %d)", who, world);
+    if (rank < 0 || rank >= world) return set_error(MT_EINVAL, "%s: rank %d out of range", who, rank);
+    if (!grad_bases || !param_bases) return set_error(MT_EINVAL, "%s: peer base arrays are NULL", who);
+    for (int r = 0; r < world; r++)
+        if (!grad_bases[r] || !param_bases[r]) return set_error(MT_EINVAL, "%s: peer %d base pointer is NULL", who, r);
+    if ((grad_multicast == nullptr) != (param_multicast == nullptr))
+        return set_error(MT_EINVAL, "%s: give both multicast addresses or neither", who);
+    for (int d = 0; d < 3; d++)
+        if (tl->dtype[d] != MT_F32) return set_error(MT_EINVAL, "%s: p, m, v must be float32", who);
+    if (tl->dtype[4] != tl->dtype[3]) return set_error(MT_EINVAL, "%s: p_copy must have the gradient dtype", who);
+    if (tl->dtype[3] != MT_BF16 && tl->dtype[3] != MT_F16)
+        return set_error(MT_EINVAL, "%s: gradients must be bf16 or fp16", who);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(tl->device);
+    if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    const bool mc = grad_multicast != nullptr;
+    typename DistAdamOp<__nv_bfloat16, true, true>::Params base{per_tensor_beta1, per_tensor_beta2, per_tensor_eps,
+                                                                per_tensor_weight_decay, per_tensor_bias_correction,
+                                                                lr, grad_scale, step, mode};
+    // Occupancy: the peer stream needs many bytes in flight (NVLink latency is ~3.5x HBM's), so the register budget
+    // shrinks with the number of peers loaded per thread: 4 CTAs/SM for multicast and 2 ranks, 3 for 4 ranks, 2 for 8.
+#define MT_P2P(TG, W, MC, MB)                                                                                            {                                                                                                                        typename DistAdamOp<TG, true, true>::Params b2;                                                                      static_assert(sizeof(b2) == sizeof(base), "Params layout is independent of the gradient type");                      memcpy(&b2, &base, sizeof(b2));                                                                                      return launch_p2p<TG, W, MC, MB>(tb, b2, rank, grad_bases, param_bases, grad_multicast, param_multicast,                                              noop_flag, tl->device, stream);                                                 }
+#define MT_P2P_W(TG)                                          if (mc) {                                                     if (world == 2) MT_P2P(TG, 2, true, 4)                    if (world == 4) MT_P2P(TG, 4, true, 4)                    MT_P2P(TG, 8, true, 4)                                } else {                                                      if (world == 2) MT_P2P(TG, 2, false, 4)                   if (world == 4) MT_P2P(TG, 4, false, 3)                   MT_P2P(TG, 8, false, 2)                               }
+    if (tl->dtype[3] == MT_BF16) { MT_P2P_W(__nv_bfloat16) } else { MT_P2P_W(__half) }
+#undef MT_P2P_W
+#undef MT_P2P
+}

@@ -250,6 +250,8 @@ template <int THREADS> __device__ __forceinline__ float block_sum(float v, float
 //   __device__ void begin_tensor(int t);         per-tile, uniform: fetch per-tensor scalars
 //   __device__ bool load(int d) / store(int d);  runtime (uniform) refinement of kRead / kWrite
 //   __device__ void elem(float (&x)[kLists], State&);   one element: inputs in x, outputs written to x
+//   static constexpr unsigned kCustomLoad, kCustomStore;  + custom_load<D,G,kVec>() / custom_store<D,G,kVec>()
+//                                                (lists the Op moves itself, e.g. over NVLink peer pointers)
 //   template <int THREADS> __device__ void end_tile_n(uint32_t tile, State&, float* smem, int32_t* noop);
 //                                                (norm ops: block reduce + per-tile partial + flag)
 //   __device__ void finish(State&, int32_t* noop);                  (flag ops)
@@ -264,7 +266,8 @@ __device__ __forceinline__ void load_list(const Op& op, char* const (&base)[Op::
         if (op.load(D)) {
             const T* p = reinterpret_cast<const T*>(base[D]) + idx;
             constexpr bool RO = ((Op::kWrite >> D) & 1u) == 0;
-            if constexpr (kVec) Group<T, G, RO>::ld(p, x[D]);
+            if constexpr (((Op::kCustomLoad >> D) & 1u) != 0) op.template custom_load<D, G, kVec>(p, x[D]);
+            else if constexpr (kVec) Group<T, G, RO>::ld(p, x[D]);
             else x[D][0] = Elem<T>::load(p);
             return;
         }
@@ -280,7 +283,8 @@ __device__ __forceinline__ void store_list(const Op& op, char* const (&base)[Op:
     if constexpr (((Op::kWrite >> D) & 1u) != 0) {
         if (op.store(D)) {
             T* p = reinterpret_cast<T*>(base[D]) + idx;
-            if constexpr (kVec) Group<T, G, false>::st(p, x[D]);
+            if constexpr (((Op::kCustomStore >> D) & 1u) != 0) op.template custom_store<D, G, kVec>(p, x[D]);
+            else if constexpr (kVec) Group<T, G, false>::st(p, x[D]);
             else Elem<T>::store(p, x[D][0]);
         }
     }
@@ -415,6 +419,8 @@ mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __res
 struct OpBase {
     struct State {};
     static constexpr bool kEarlyExit = false;
+    // bit d set: list d is moved by the Op's own custom_load / custom_store (peer-memory ops) instead of Group<>
+    static constexpr unsigned kCustomLoad = 0, kCustomStore = 0;
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void begin_tensor(int) {}
     __device__ __forceinline__ bool load(int) const { return true; }

@@ -128,6 +128,130 @@ template <class Tg, bool kCopy, bool kHonourNoop> struct DistAdamOp : OpBase {
     }
 };
 
+// Fused reduce-scatter + DistAdam + all-gather over peer memory (NVLink P2P through NVSwitch).  Same arithmetic as
+// DistAdamOp; list 3 (gradients) is READ FROM EVERY RANK'S buffer and summed in rank order, list 4 (updated 16-bit
+// params) is WRITTEN TO EVERY RANK'S buffer.  The tensor table holds this rank's own pointers; a peer's address is
+// base[r] + (own pointer - base[rank]) because the buffers are symmetric allocations.  The sum is rounded to Tg once,
+// which is what a reduce-scatter producing Tg gradients delivers, so the result matches the NCCL route bit for bit
+// whenever the inputs' sum is exact in Tg.
+template <class Tg> struct Packed16;  // two 16-bit elements in one 32-bit word
+template <> struct Packed16<__nv_bfloat16> {
+    __device__ static __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
+        lo = __uint_as_float(w << 16);
+        hi = __uint_as_float(w & 0xffff0000u);
+    }
+};
+template <> struct Packed16<__half> {
+    __device__ static __forceinline__ void unpack(uint32_t w, float& lo, float& hi) {
+        const float2 t = __half22float2(*reinterpret_cast<const __half2*>(&w));
+        lo = t.x;
+        hi = t.y;
+    }
+};
+
+// NVSwitch multicast (multimem.*) accesses on a multicast address: one instruction reduces across / stores to every
+// GPU of the multicast group inside the switch (NVLS), so each gradient byte crosses this GPU's link once instead of
+// once per peer.
+template <class Tg> struct Multimem;
+template <> struct Multimem<__nv_bfloat16> {
+    __device__ static __forceinline__ void ld_reduce(const void* mc, uint32_t (&w)[4]) {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(mc) : "memory");
+    }
+};
+template <> struct Multimem<__half> {
+    __device__ static __forceinline__ void ld_reduce(const void* mc, uint32_t (&w)[4]) {
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(mc) : "memory");
+    }
+};
+__device__ __forceinline__ void multimem_st_16B(void* mc, const uint32_t (&w)[4]) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                 "r"(w[3]) : "memory");
+}
+
+// kMc = false: peer-to-peer loads / stores on every rank's mapped buffer.
+// kMc = true : the 8-element vector path goes through the multicast address (in-switch reduction and broadcast);
+//              the scalar head / tail elements still use the per-peer pointers.
+template <class Tg, int WORLD, bool kMc> struct DistAdamP2POp : DistAdamOp<Tg, true, true> {
+    using Base = DistAdamOp<Tg, true, true>;
+    static constexpr unsigned kCustomLoad = 0b01000, kCustomStore = 0b10000;
+    struct Params {
+        typename Base::Params base;
+        const char* gbase[WORLD];  // every rank's flat gradient buffer, as mapped in THIS process
+        char* pbase[WORLD];        // every rank's flat parameter buffer
+        const char* gown;          // = gbase[rank], pbase[rank]: passed separately so that the arrays are only ever
+        char* pown;                //   indexed by compile-time constants (a runtime index would spill them to local memory)
+        const char* gmc;           // multicast addresses of the two buffers (kMc only)
+        char* pmc;
+    };
+    Params q;
+    __device__ explicit DistAdamP2POp(const Params& prm) : Base(prm.base), q(prm) {}
+    template <int D, int G, bool kVec>
+    __device__ __forceinline__ void custom_load(const Tg* p, float (&x)[G]) const {
+        static_assert(D == 3, "only the gradient list is gathered");
+        const ptrdiff_t off = reinterpret_cast<const char*>(p) - q.gown;
+        if constexpr (kVec) {
+            static_assert(G == 8, "vector path moves 8 x 16-bit = 16 bytes");
+            if constexpr (kMc) {
+                uint32_t w[4];
+                Multimem<Tg>::ld_reduce(q.gmc + off, w);  // sum over all ranks, fp32 accumulate, rounded once to Tg
+#pragma unroll
+                for (int i = 0; i < 4; i++) Packed16<Tg>::unpack(w[i], x[2 * i], x[2 * i + 1]);
+            } else {
+                uint32_t w[WORLD][4];
+#pragma unroll
+                for (int r = 0; r < WORLD; r++) RawVec<4, true>::ld(q.gbase[r] + off, w[r]);  // all peers in flight
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    float lo, hi;
+                    Packed16<Tg>::unpack(w[0][i], lo, hi);
+#pragma unroll
+                    for (int r = 1; r < WORLD; r++) {
+                        float l2, h2;
+                        Packed16<Tg>::unpack(w[r][i], l2, h2);
+                        lo = fadd(lo, l2);
+                        hi = fadd(hi, h2);
+                    }
+                    x[2 * i] = Elem<Tg>::round(lo);
+                    x[2 * i + 1] = Elem<Tg>::round(hi);
+                }
+            }
+        } else {
+            float acc = Elem<Tg>::load(reinterpret_cast<const Tg*>(q.gbase[0] + off));
+#pragma unroll
+            for (int r = 1; r < WORLD; r++) acc = fadd(acc, Elem<Tg>::load(reinterpret_cast<const Tg*>(q.gbase[r] + off)));
+            x[0] = Elem<Tg>::round(acc);
+        }
+    }
+    template <int D, int G, bool kVec>
+    __device__ __forceinline__ void custom_store(Tg* p, const float (&x)[G]) const {
+        static_assert(D == 4, "only the parameter copy is scattered");
+        const ptrdiff_t off = reinterpret_cast<const char*>(p) - q.pown;
+        if constexpr (kVec && kMc) {
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if constexpr (std::is_same<Tg, __nv_bfloat16>::value) {
+                    __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+                    w[i] = *reinterpret_cast<uint32_t*>(&h);
+                } else {
+                    __half2 h = __floats2half2_rn(x[2 * i], x[2 * i + 1]);
+                    w[i] = *reinterpret_cast<uint32_t*>(&h);
+                }
+            }
+            multimem_st_16B(q.pmc + off, w);
+        } else {
+#pragma unroll
+            for (int r = 0; r < WORLD; r++) {
+                Tg* dst = reinterpret_cast<Tg*>(q.pbase[r] + off);
+                if constexpr (kVec) Group<Tg, G, false>::st(dst, x);
+                else Elem<Tg>::store(dst, x[0]);
+            }
+        }
+    }
+};
+
 // ------------------------------------------------------------------------------------------------
 // SGDFunctor: csrc/multi_tensor_sgd_kernel.cu:87-134.   lists: g, w, mom [, fp16 model copy]
 template <class Tg, class Tw, bool kCopy> struct SgdOp : OpBase {

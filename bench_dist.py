@@ -43,9 +43,17 @@ def run_distributed(args, rank, world, local_rank, device):
     shapes = workloads.WORKLOADS[args.workload]()
     numels = workloads.numels(shapes)
     P = sum(numels)
-    opt = DistributedFusedAdam(numels=numels, lr=HP["lr"], betas=(HP["beta1"], HP["beta2"]), eps=HP["eps"],
-                               weight_decay=HP["wd"], adam_w_mode=True, device=device, bucket_cap_mb=1024.0,
-                               grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16)
+    kw = dict(numels=numels, lr=HP["lr"], betas=(HP["beta1"], HP["beta2"]), eps=HP["eps"], weight_decay=HP["wd"],
+              adam_w_mode=True, device=device, bucket_cap_mb=1024.0, grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16)
+    fused_err = None
+    try:  # symmetric-memory buffers: enables the single-kernel reduce-scatter + update + all-gather route
+        opt = DistributedFusedAdam(fused_p2p=True, **kw)
+    except Exception as e:  # noqa: BLE001
+        fused_err = repr(e)[:300]
+        opt = DistributedFusedAdam(fused_p2p=False, **kw)
+    ok = torch.tensor([1 if opt.fused_p2p else 0], device=device)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    fused = bool(ok.item())
     L = opt.layout
     if rank == 0:
         log(f"[bench] {args.workload}: {len(numels)} tensors, {P} params; world={world}, {L.nbuckets} buckets of "
@@ -61,12 +69,36 @@ def run_distributed(args, rank, world, local_rank, device):
     torch.cuda.synchronize(device)
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    # NCCL route (reduce_scatter -> update -> all_gather on three streams)
     for _ in range(args.warmup):
         opt.step()
     launches0 = amp_C.launch_count()
-    ms, t0, t1 = _timed(opt.step, args.steps, device)
+    ms_nccl, t0, t1 = _timed(opt.step, args.steps, device)
     launches = amp_C.launch_count() - launches0
     clocks = ClockSampler.summarize(sampler.window(t0, t1)) if sampler else None
+    ms, route, ms_fused = ms_nccl, "nccl: reduce_scatter -> update -> all_gather, 3 streams", None
+    ms_p2p = ms_mc = None
+    fused_fn = None
+    if fused:
+        # fused route: one kernel reads the gradient shard from every peer and writes the parameters to every peer
+        for _ in range(args.warmup):
+            opt.step_fused()
+        launches0 = amp_C.launch_count()
+        ms_p2p, t0f, t1f = _timed(lambda: opt.step_fused(multicast=False), args.steps, device)
+        n_l = amp_C.launch_count() - launches0
+        ms_fused, fused_fn = ms_p2p, (lambda: opt.step_fused(multicast=False))
+        fused_name = "fused_p2p: one kernel, ld/st on every peer's buffer over NVLink (+2 barriers)"
+        if opt.has_multicast:
+            for _ in range(args.warmup):
+                opt.step_fused(multicast=True)
+            ms_mc, t0m, t1m = _timed(lambda: opt.step_fused(multicast=True), args.steps, device)
+            if ms_mc < ms_p2p:
+                ms_fused, fused_fn, t0f, t1f = ms_mc, (lambda: opt.step_fused(multicast=True)), t0m, t1m
+                fused_name = "fused_multicast: one kernel, multimem.ld_reduce / multimem.st through NVSwitch (+2 barriers)"
+        if ms_fused < ms_nccl:
+            ms, route = ms_fused, fused_name
+            launches = n_l
+            clocks = ClockSampler.summarize(sampler.window(t0f, t1f)) if sampler else clocks
 
     # breakdown (each max over ranks)
     ms_update, _, _ = _timed(lambda: [opt._update_bucket(b, float(world)) for b in range(L.nbuckets)], args.steps, device)
@@ -90,7 +122,7 @@ def run_distributed(args, rank, world, local_rank, device):
             for o in range(0, L.padded, win):
                 n = min(win, L.padded - o)
                 opt.grads_flat[o:o + n].copy_(host[:n], non_blocking=True)
-            opt.step()
+            (fused_fn if (fused_fn is not None and ms_fused < ms_nccl) else opt.step)()
             host_flag.copy_(opt.noop, non_blocking=True)
             torch.cuda.current_stream(device).synchronize()
 
@@ -113,12 +145,15 @@ def run_distributed(args, rank, world, local_rank, device):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload}: ZeRO-2 sharded mixed-precision AdamW ({P} params, {len(numels)} tensors): "
                                    f"reduce-scatter bf16 grads -> shard update (fp32 p/m/v) -> all-gather bf16 params",
-                       "parallelism": f"optimizer state sharded x{world}, {L.nbuckets} buckets pipelined on 3 streams",
+                       "parallelism": f"optimizer state sharded x{world}; route = {route}",
                        "bytes_per_param": BYTES_PER_PARAM, "l2": "inputs >> L2; no flush needed", "hyper": HP},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "mt_table_kernel<DistAdamOp<bf16,copy,noop>> (shard update only)",
                          "algorithmic_bytes_per_launch": shard_bytes / max(1, L.nbuckets)},
-            "breakdown_ms": {"step_overlapped": ms, "step_serial": ms_serial, "update_only": ms_update,
+            "route": route, "fused_p2p_error": fused_err,
+            "breakdown_ms": {"step": ms, "step_nccl_overlapped": ms_nccl, "step_fused_p2p": ms_p2p,
+                             "step_fused_multicast": ms_mc,
+                             "step_nccl_serial": ms_serial, "update_only": ms_update,
                              "reduce_scatter_only": ms_rs, "all_gather_only": ms_ag},
             "update_only": {"params_per_s_whole_job": P / (ms_update * 1e-3), "hbm_gbs_per_gpu": achieved},
             "nvlink": {"bytes_sent_per_gpu_per_collective": nvlink_bytes,

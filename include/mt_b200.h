@@ -138,6 +138,24 @@ int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTenso
                                const float* per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
                                int honour_noop, void* stream);
 
+/* Fused gradient reduce-scatter + sharded Adam + parameter all-gather in one kernel over NVLink peer memory.
+ * Same arithmetic and lists as mt_multi_tensor_fused_adam with p_copy ([p, m, v, g, p_copy], honour_noop on), but list 3
+ * is read from EVERY rank's gradient buffer (summed in rank order, rounded once to the gradient dtype) and list 4 is
+ * written to EVERY rank's parameter buffer.  grad_bases[r] / param_bases[r] are rank r's flat buffers as mapped into
+ * this process (symmetric allocations of identical layout); tl's lists 3 and 4 point into grad_bases[rank] /
+ * param_bases[rank].  world is 2, 4 or 8.  grad_multicast / param_multicast: NVSwitch multicast addresses of the same
+ * two buffers (both or neither; NULL = plain peer-to-peer).  With them the 16-byte vector path uses
+ * multimem.ld_reduce / multimem.st, i.e. the sum and the broadcast happen inside the switch.  The caller runs a
+ * cross-GPU barrier before (all gradients complete) and after (all parameter writes landed) the call.
+ * Replaces the reduce_scatter -> multi_tensor_fused_adam -> all_gather sequence of
+ * /root/reference/apex/contrib/optimizers/distributed_fused_adam.py:668-742,977-1115. */
+int mt_multi_tensor_fused_adam_p2p(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                   const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                   const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                   const float* per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
+                                   int world, int rank, const void* const* grad_bases, void* const* param_bases,
+                                   const void* grad_multicast, void* param_multicast, void* stream);
+
 /* L2 norm for callers that cannot allocate.  No counterpart in the reference (its multi_tensor_l2norm_cuda allocates
  * four tensors per call through torch).
  *

@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 SIZES = [1000, 7, 4096, 33333, 1, 129, 300001]
 
 
-def _worker(rank, world, port, outdir):
+def _worker(rank, world, port, outdir, fused=False):
     import torch.distributed as dist
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
@@ -23,7 +23,10 @@ def _worker(rank, world, port, outdir):
 
         wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
         opt = DistributedFusedAdam(numels=SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, device=f"cuda:{rank}",
-                                   bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds)
+                                   bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds, fused_p2p=bool(fused))
+        if fused == "mc" and not opt.has_multicast:
+            torch.save({"skip": "no NVSwitch multicast on this box"}, os.path.join(outdir, f"rank{rank}.pt"))
+            return
         L = opt.layout
         assert L.nbuckets > 1
         torch.manual_seed(0)
@@ -34,10 +37,13 @@ def _worker(rank, world, port, outdir):
             opt.zero_grad()
             g = torch.Generator().manual_seed(100 * it + rank)
             for n, o in zip(SIZES, L.offsets):
-                # multiples of 2^-10 in [-4, 4): sums of two are exact in bf16
-                opt.grads_flat[o:o + n].copy_((torch.randint(-64, 64, (n,), generator=g).float() / 1024))
-            opt.step()
-        gn = opt.grad_norm()
+                # small multiples of 2^-10: sums over up to 8 ranks are exact in bf16
+                opt.grads_flat[o:o + n].copy_((torch.randint(-16, 16, (n,), generator=g).float() / 1024))
+            if fused:
+                opt.step_fused(multicast=(fused == "mc"))
+            else:
+                opt.step()
+        gn = opt.grad_norm() if not fused else torch.zeros(1)
         torch.cuda.synchronize()
         out = [opt.params_flat[o:o + n].cpu().clone() for n, o in zip(SIZES, L.offsets)]
         torch.save({"params": out, "noop": int(opt.noop.item()), "gn": float(gn.item())}, os.path.join(outdir, f"rank{rank}.pt"))
@@ -54,24 +60,27 @@ def _free_port():
 
 
 @pytest.mark.timeout(600)
-def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
+@pytest.mark.parametrize("fused", [False, "p2p", "mc"], ids=["nccl", "fused_p2p", "fused_multicast"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle, fused, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
 
-    world = 2
     ctx = mp.get_context("spawn")
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), fused)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
         p.join(500)
         assert p.exitcode == 0
     res = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
+    if "skip" in res[0]:
+        pytest.skip(res[0]["skip"])
     for a, b in zip(res[0]["params"], res[1]["params"]):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
-    assert res[0]["noop"] == 0 and abs(res[0]["gn"] - res[1]["gn"]) <= 1e-6 * res[0]["gn"]
+    assert res[0]["noop"] == 0 and abs(res[0]["gn"] - res[1]["gn"]) <= 1e-6 * max(res[0]["gn"], 1e-30)
 
     torch.manual_seed(0)
     p32 = [(torch.randn(n) * 0.02).bfloat16().float() for n in SIZES]
@@ -85,7 +94,7 @@ def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle):
         for r in range(world):
             g = torch.Generator().manual_seed(100 * it + r)
             for i, n in enumerate(SIZES):
-                gs[i] += torch.randint(-64, 64, (n,), generator=g).float() / 1024
+                gs[i] += torch.randint(-16, 16, (n,), generator=g).float() / 1024
         gs = [x.bfloat16() for x in gs]
         oracle.multi_tensor_fused_adam(8192, torch.zeros(1, dtype=torch.int32), [p32, m, v, gs, pc], [0.9] * k, [0.95] * k,
                                        [1] * k, [1e-8] * k, wds, 1e-2, float(world), it + 1, 1)
