@@ -141,7 +141,8 @@ void multi_tensor_axpby(int chunk_size, at::Tensor noop_flag, TensorLists tensor
 }
 
 std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_flag, const py::object& tensor_lists,
-                                               bool with_scale, float scale, at::optional<bool> per_tensor_python) {
+                                               bool with_scale, float scale, at::optional<bool> per_tensor_python,
+                                               bool mp = false) {
     const bool per_tensor = per_tensor_python.has_value() ? per_tensor_python.value() : false;
     Flat f;
     flatten(tensor_lists, with_scale ? 2 : 1, with_scale ? 2 : 1, with_scale ? "multi_tensor_l2norm_scale" : "multi_tensor_l2norm", f);
@@ -156,6 +157,10 @@ std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_f
         rc = mt_multi_tensor_l2norm_scale(chunk_size, flag_ptr(noop_flag), &f.tl, scale, per_tensor,
                                           ret.data_ptr<float>(), per_tensor ? ret_per_tensor.data_ptr<float>() : nullptr,
                                           scratch.data_ptr(), sbytes, f.stream);
+    else if (mp)
+        rc = mt_multi_tensor_l2norm_mp(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor, ret.data_ptr<float>(),
+                                       per_tensor ? ret_per_tensor.data_ptr<float>() : nullptr, scratch.data_ptr(), sbytes,
+                                       f.stream);
     else
         rc = mt_multi_tensor_l2norm(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor, ret.data_ptr<float>(),
                                     per_tensor ? ret_per_tensor.data_ptr<float>() : nullptr, scratch.data_ptr(), sbytes,
@@ -173,6 +178,32 @@ std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm_scale(int chunk_size, at:
                                                              TensorLists tensor_lists, float scale,
                                                              at::optional<bool> per_tensor_python) {
     return l2norm_impl(chunk_size, noop_flag, tensor_lists, true, scale, per_tensor_python);
+}
+
+std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm_mp(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                                          at::optional<bool> per_tensor_python) {
+    return l2norm_impl(chunk_size, noop_flag, tensor_lists, false, 0.f, per_tensor_python, true);
+}
+
+void multi_tensor_lamb_mp(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, at::Tensor lr, const float beta1,
+                          const float beta2, const float epsilon, at::Tensor step, const int bias_correction,
+                          const float weight_decay, const int grad_averaging, const int mode, at::Tensor global_grad_norm,
+                          at::Tensor max_grad_norm, at::optional<bool> use_nvlamb_python, at::Tensor found_inf,
+                          at::Tensor inv_scale) {
+    const bool use_nvlamb = use_nvlamb_python.has_value() ? use_nvlamb_python.value() : false;
+    Flat f;
+    flatten(tensor_lists, 4, 5, "multi_tensor_lamb_mp", f);
+    TORCH_CHECK(lr.is_cuda() && lr.scalar_type() == at::kFloat && step.is_cuda() && step.scalar_type() == at::kInt &&
+                    global_grad_norm.is_cuda() && max_grad_norm.is_cuda() && inv_scale.is_cuda() && found_inf.is_cuda(),
+                "multi_tensor_lamb_mp: lr (float), step (int), global_grad_norm, max_grad_norm, found_inf, inv_scale must be CUDA tensors");
+    const c10::cuda::CUDAGuard guard(f.device);
+    const size_t sbytes = mt_lamb_scratch_bytes(chunk_size, &f.tl);
+    at::Tensor scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)}, f.first.options().dtype(at::kByte).layout(at::kStrided));
+    check(mt_multi_tensor_lamb_mp(chunk_size, flag_ptr(noop_flag), &f.tl, lr.data_ptr<float>(), beta1, beta2, epsilon,
+                                  step.data_ptr<int32_t>(), bias_correction, weight_decay, grad_averaging, mode,
+                                  global_grad_norm.data_ptr<float>(), max_grad_norm.data_ptr<float>(), use_nvlamb,
+                                  found_inf.data_ptr<float>(), inv_scale.data_ptr<float>(), scratch.data_ptr(), sbytes,
+                                  f.stream));
 }
 
 void multi_tensor_adam(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
@@ -234,6 +265,45 @@ void multi_tensor_lamb_stage2_cuda(int chunk_size, at::Tensor noop_flag, TensorL
     flatten(tensor_lists, 2, 2, "multi_tensor_lamb_stage2_cuda", f);
     check(mt_multi_tensor_lamb_stage2(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_param_norm.data_ptr<float>(),
                                       per_tensor_update_norm.data_ptr<float>(), lr, weight_decay, use_nvlamb, f.stream));
+}
+
+void multi_tensor_adagrad(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
+                          const float epsilon, const int mode, const float weight_decay) {
+    Flat f;
+    flatten(tensor_lists, 3, 3, "multi_tensor_adagrad", f);
+    check(mt_multi_tensor_adagrad(chunk_size, flag_ptr(noop_flag), &f.tl, lr, epsilon, mode, weight_decay, f.stream));
+}
+
+void multi_tensor_novograd(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, at::Tensor grad_norms,
+                           const float lr, const float beta1, const float beta2, const float epsilon, const int step,
+                           const int bias_correction, const float weight_decay, const int grad_averaging,
+                           const int mode, const int norm_type) {
+    Flat f;
+    flatten(tensor_lists, 3, 3, "multi_tensor_novograd", f);
+    TORCH_CHECK(grad_norms.is_cuda() && grad_norms.scalar_type() == at::kFloat && grad_norms.numel() >= f.tl.ntensors,
+                "grad_norms must be a CUDA float tensor with one entry per tensor");
+    TORCH_CHECK(f.first.device() == noop_flag.device(), "noop flag should be on the same device as tensors");
+    const c10::cuda::CUDAGuard guard(f.device);
+    const size_t sbytes = mt_norm_scratch_bytes(chunk_size, &f.tl);
+    at::Tensor scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)}, f.first.options().dtype(at::kByte).layout(at::kStrided));
+    check(mt_multi_tensor_novograd(chunk_size, flag_ptr(noop_flag), &f.tl, grad_norms.data_ptr<float>(), lr, beta1, beta2,
+                                   epsilon, step, bias_correction, weight_decay, grad_averaging, mode, norm_type,
+                                   scratch.data_ptr(), sbytes, f.stream));
+}
+
+void multi_tensor_lars(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, at::Tensor grad_norms,
+                       at::Tensor param_norms, float lr, float trust_coefficient, float epsilon, float weight_decay,
+                       float momentum, float dampening, bool nesterov, bool first_run, bool wd_after_momentum, float scale,
+                       const bool is_skipped) {
+    Flat f;
+    flatten(tensor_lists, 3, 4, "multi_tensor_lars", f);
+    if (f.tl.depth == 4) TORCH_CHECK(f.tl.dtype[3] == MT_F16, "Additional output tensors should always be fp16.");
+    TORCH_CHECK(noop_flag.device() == f.first.device(), "expected noop flag to be on the same device as tensors");
+    TORCH_CHECK(grad_norms.is_cuda() && param_norms.is_cuda() && grad_norms.scalar_type() == at::kFloat &&
+                    param_norms.scalar_type() == at::kFloat, "grad_norms / param_norms must be CUDA float tensors");
+    check(mt_multi_tensor_lars(chunk_size, flag_ptr(noop_flag), &f.tl, grad_norms.data_ptr<float>(),
+                               param_norms.data_ptr<float>(), lr, trust_coefficient, epsilon, weight_decay, momentum,
+                               dampening, nesterov, first_run, wd_after_momentum, scale, is_skipped, f.stream));
 }
 
 // distributed_adam_cuda.multi_tensor_fused_adam
@@ -305,6 +375,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("multi_tensor_sgd", &multi_tensor_sgd, "Fused SGD optimizer for list of contiguous tensors");
     m.def("multi_tensor_axpby", &multi_tensor_axpby, "out = a*x + b*y for a list of contiguous tensors");
     m.def("multi_tensor_l2norm", &multi_tensor_l2norm, "Computes L2 norm for a list of contiguous tensors");
+    m.def("multi_tensor_l2norm_mp", &multi_tensor_l2norm_mp, "Computes L2 norm for a list of contiguous tensors");
+    m.def("multi_tensor_lamb_mp", &multi_tensor_lamb_mp, "Computes and apply update for LAMB optimizer");
     m.def("multi_tensor_l2norm_scale", &multi_tensor_l2norm_scale,
           "Computes L2 norm for a list of contiguous tensors and does scaling");
     m.def("multi_tensor_lamb_stage1_cuda", &multi_tensor_lamb_stage1_cuda, "Computes update part of LAMB optimizer");
@@ -312,6 +384,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           "Completes application of gradient to parameters for LAMB optimizer");
     m.def("multi_tensor_adam", &multi_tensor_adam, "Compute and apply gradient update to parameters for Adam optimizer");
     m.def("multi_tensor_lamb", &multi_tensor_lamb, "Computes and apply update for LAMB optimizer");
+    m.def("multi_tensor_adagrad", &multi_tensor_adagrad, "Compute and apply gradient update to parameters for Adagrad optimizer");
+    m.def("multi_tensor_novograd", &multi_tensor_novograd, "Compute and apply gradient update to parameters for NovoGrad optimizer");
+    m.def("multi_tensor_lars", &multi_tensor_lars, "Fused LARS optimizer for list of contiguous tensors");
     m.def("multi_tensor_fused_adam", &multi_tensor_fused_adam, "Mixed-precision / sharded Adam (DistAdamFunctor)",
           py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor_beta1"),
           py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),

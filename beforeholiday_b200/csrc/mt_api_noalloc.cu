@@ -32,7 +32,7 @@
 namespace mt {
 
 int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
-                         int device, cudaStream_t stream);  // mt_api_norm.cu
+                         int device, cudaStream_t stream, const int32_t* skip_if_set = nullptr);  // mt_api_norm.cu
 
 namespace {
 
@@ -125,7 +125,7 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
 
     constexpr int G = 8, U = 2, THREADS = 256, MINB = 4;  // same shape as mt_multi_tensor_l2norm
     MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
-        using Op = L2NormOp<Tx>;
+        using Op = L2NormOp<Tx, false>;
         typename Op::Params prm{partials};
         rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
     })

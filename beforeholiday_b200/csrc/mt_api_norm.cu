@@ -18,8 +18,10 @@ constexpr int kFinThreads = 512;
 __global__ void __launch_bounds__(kFinThreads)
 norm_finalize_kernel(const float* __restrict__ partials, int nsets, uint32_t ntiles,
                      const uint32_t* __restrict__ tile_begin, int ntensors, float* __restrict__ ret_global,
-                     float* __restrict__ ret_pt) {
+                     float* __restrict__ ret_pt, const int32_t* __restrict__ skip_if_set) {
     __shared__ float smem[kFinThreads / 32];
+    // "_mp" variants: leave the outputs untouched when the flag is set (csrc/multi_tensor_l2norm_kernel_mp.cu:121-123)
+    if (skip_if_set && *reinterpret_cast<const volatile int32_t*>(skip_if_set) != 0) return;
     if (blockIdx.x == 0 && ret_global) {
         for (int s = 0; s < nsets; s++) {
             float acc = 0.f;
@@ -44,7 +46,7 @@ norm_finalize_kernel(const float* __restrict__ partials, int nsets, uint32_t nti
 }
 
 int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
-                         int device, cudaStream_t stream) {
+                         int device, cudaStream_t stream, const int32_t* skip_if_set) {
     DeviceInfo di;
     int rc = device_info(device, &di);
     if (rc) return rc;
@@ -56,14 +58,14 @@ int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, f
         grid = (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
     }
     norm_finalize_kernel<<<grid, kFinThreads, 0, stream>>>(partials, nsets, tb.ntiles, tb.tile_begin, tb.ntensors,
-                                                           ret_global, ret_pt);
+                                                           ret_global, ret_pt, skip_if_set);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     MT_CUDA_OK(cudaGetLastError());
     return MT_OK;
 }
 
 static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int depth,
-                       float scale, int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
+                       bool mp, float scale, int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
                        size_t scratch_bytes, cudaStream_t stream) {
     int rc = validate_lists(tl, depth, depth, who);
     if (rc) return rc;
@@ -83,9 +85,15 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     constexpr int G = 8, U = 2, THREADS = 256, MINB = 4;
     if (depth == 1) {
         MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
-            using Op = L2NormOp<Tx>;
-            typename Op::Params prm{partials};
-            rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+            if (mp) {
+                using Op = L2NormOp<Tx, true>;
+                typename Op::Params prm{partials};
+                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+            } else {
+                using Op = L2NormOp<Tx, false>;
+                typename Op::Params prm{partials};
+                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+            }
         })
     } else {
         MT_DISPATCH_FHB(tl->dtype[0], Tin, who,
@@ -96,7 +104,8 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
             }))
     }
     if (rc) return rc;
-    return launch_norm_finalize(tb, partials, 1, ret, per_tensor ? ret_per_tensor : nullptr, tl->device, stream);
+    return launch_norm_finalize(tb, partials, 1, ret, per_tensor ? ret_per_tensor : nullptr, tl->device, stream,
+                                mp ? noop_flag : nullptr);
 }
 
 }  // namespace mt
@@ -109,13 +118,20 @@ extern "C" size_t mt_norm_scratch_bytes(int chunk_size, const MtTensorLists* tl)
 extern "C" int mt_multi_tensor_l2norm(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
                                       float* ret, float* ret_per_tensor, void* scratch, size_t scratch_bytes,
                                       void* stream) {
-    return mt::norm_common("multi_tensor_l2norm", chunk_size, noop_flag, tl, 1, 0.f, per_tensor, ret, ret_per_tensor,
+    return mt::norm_common("multi_tensor_l2norm", chunk_size, noop_flag, tl, 1, false, 0.f, per_tensor, ret, ret_per_tensor,
                            scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int mt_multi_tensor_l2norm_scale(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float scale,
                                             int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
                                             size_t scratch_bytes, void* stream) {
-    return mt::norm_common("multi_tensor_l2norm_scale", chunk_size, noop_flag, tl, 2, scale, per_tensor, ret,
+    return mt::norm_common("multi_tensor_l2norm_scale", chunk_size, noop_flag, tl, 2, false, scale, per_tensor, ret,
+                           ret_per_tensor, scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mt_multi_tensor_l2norm_mp(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
+                                         float* ret, float* ret_per_tensor, void* scratch, size_t scratch_bytes,
+                                         void* stream) {
+    return mt::norm_common("multi_tensor_l2norm_mp", chunk_size, noop_flag, tl, 1, true, 0.f, per_tensor, ret,
                            ret_per_tensor, scratch, scratch_bytes, static_cast<cudaStream_t>(stream));
 }

@@ -7,7 +7,7 @@
 namespace mt {
 
 int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
-                         int device, cudaStream_t stream);  // mt_api_norm.cu
+                         int device, cudaStream_t stream, const int32_t* skip_if_set = nullptr);  // mt_api_norm.cu
 
 // Host-side bias corrections: /root/reference/csrc/multi_tensor_adam.cu:145-149.  std::pow(float, int)
 // promotes to double; the result is rounded to float.
@@ -190,6 +190,64 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
         return launch_table_kernel<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);
     })
     return MT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+extern "C" int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, const float* lr,
+                                       float beta1, float beta2, float epsilon, const int32_t* step, int bias_correction,
+                                       float weight_decay, int grad_averaging, int mode, const float* global_grad_norm,
+                                       const float* max_grad_norm, int use_nvlamb, const float* found_inf,
+                                       const float* inv_scale, void* scratch, size_t scratch_bytes, void* stream_) {
+    MT_PROLOGUE("multi_tensor_lamb_mp", 4, 5)
+    (void)found_inf;  // carried for signature compatibility; the reference functor never reads it either
+    if (!lr || !step || !global_grad_norm || !max_grad_norm || !inv_scale)
+        return set_error(MT_EINVAL, "multi_tensor_lamb_mp: lr, step, global_grad_norm, max_grad_norm, inv_scale must be device pointers");
+    const int gt = tl->dtype[0], pt = tl->dtype[1];
+    if (tl->dtype[2] != pt || tl->dtype[3] != pt) return set_error(MT_EINVAL, "multi_tensor_lamb_mp: p, m, v must share one dtype");
+    const bool copy = tl->depth == 5;
+    if (copy && (pt != MT_F32 || tl->dtype[4] != gt))
+        return set_error(MT_EINVAL, "multi_tensor_lamb_mp: with 5 lists p/m/v must be float32 masters and list 4 the gradient dtype");
+    if (!copy && pt != gt) return set_error(MT_EINVAL, "multi_tensor_lamb_mp: with 4 lists all lists must share one dtype");
+    float beta3 = 1.0f;
+    if (grad_averaging == 1) beta3 = 1 - beta1;
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    const LambScratch lay = lamb_scratch_layout(tb.ntiles, tl->ntensors);
+    if (!scratch || scratch_bytes < lay.total)
+        return set_error(MT_ESCRATCH, "multi_tensor_lamb_mp: scratch too small (%zu < %zu bytes)", scratch_bytes, lay.total);
+    char* sc = static_cast<char*>(scratch);
+    float* partials = reinterpret_cast<float*>(sc + lay.off_partials);
+    float* pnorm = reinterpret_cast<float*>(sc + lay.off_pnorm);
+    float* unorm = reinterpret_cast<float*>(sc + lay.off_unorm);
+    const int need_norms = (use_nvlamb || weight_decay != 0.0f) ? 1 : 0;
+#define MT_LAMB_MP(TG, TP, COPY)                                                                                    \
+    {                                                                                                               \
+        using Op1 = LambMpStage1Op<TG, TP>;                                                                         \
+        typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm, max_grad_norm,  \
+                                inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms};                 \
+        rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);         \
+        if (rc) return rc;                                                                                          \
+        if (need_norms) {                                                                                           \
+            rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream, noop_flag);              \
+            if (rc) return rc;                                                                                      \
+        }                                                                                                           \
+        using Op2 = LambMpStage2Op<TG, TP, COPY>;                                                                   \
+        typename Op2::Params p2{pnorm, unorm, lr, weight_decay, use_nvlamb};                                        \
+        return launch_table_kernel<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);       \
+    }
+    // reference dispatch: DISPATCH_FLOAT_AND_HALF on the gradient type; bf16 is accepted here as well
+    if (copy) {
+        if (gt == MT_F16) MT_LAMB_MP(__half, float, true)
+        if (gt == MT_BF16) MT_LAMB_MP(__nv_bfloat16, float, true)
+        if (gt == MT_F32) MT_LAMB_MP(float, float, true)
+    } else {
+        if (gt == MT_F16) MT_LAMB_MP(__half, __half, false)
+        if (gt == MT_BF16) MT_LAMB_MP(__nv_bfloat16, __nv_bfloat16, false)
+        if (gt == MT_F32) MT_LAMB_MP(float, float, false)
+    }
+#undef MT_LAMB_MP
+    return set_error(MT_EINVAL, "multi_tensor_lamb_mp: unsupported gradient dtype tag %d", gt);
 }
 
 // ---------------------------------------------------------------------------------------------------

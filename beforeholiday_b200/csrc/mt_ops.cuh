@@ -294,8 +294,11 @@ struct SumState { float sum; };
 
 // L2NormFunctor: csrc/multi_tensor_l2norm_kernel.cu:56-107.  One tile == one reference chunk, so the flag
 // ("chunk partial sum is non-finite", :103-104) has the reference's granularity.   lists: x
-template <class Tx> struct L2NormOp : OpBase {
+// kMp = true is the reference's "_mp" variant (csrc/multi_tensor_l2norm_kernel_mp.cu:40-42): do nothing when the flag
+// is already set.
+template <class Tx, bool kMp = false> struct L2NormOp : OpBase {
     static constexpr int kLists = 1;
+    static constexpr bool kEarlyExit = kMp;
     template <int D> using T = Tx;
     static constexpr unsigned kRead = 0b1, kWrite = 0b0;
     struct Params { float* partials; };
@@ -408,6 +411,211 @@ template <class Tp> struct LambStage2Op : OpBase {
         }
     }
     __device__ __forceinline__ void elem(float (&x)[2], State&) const { x[1] = fsub(x[1], fmul(ratio, x[0])); }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Mixed-precision / capturable LAMB ("_mp"): csrc/multi_tensor_lamb_mp.cu:40-232 (stage 1), :234-364 (stage 2).
+// Differences from LambStage1Op: g has its own dtype Tg and is multiplied by *inv_scale first; p, m, v have dtype Tp
+// (fp32 masters or Tg); step, max_grad_norm and the learning rate are read from device memory (so a captured graph
+// replays across steps); the kernels return at once when the flag is set.
+template <class Tg, class Tp> struct LambMpStage1Op : OpBase {
+    static constexpr int kLists = 4;
+    template <int D> using T = typename Types<Tg, Tp, Tp, Tp>::template at<D>;
+    static constexpr unsigned kRead = 0b1111, kWrite = 0b1101;
+    static constexpr bool kEarlyExit = true;
+    struct Params {
+        float beta1, beta2, beta3, eps, decay;
+        const int32_t* step;
+        const float *global_grad_norm, *max_grad_norm, *inv_scale;
+        float* partials;  // [2][ntiles]
+        uint32_t ntiles;
+        int mode, bias_correction, need_norms;
+    };
+    using State = Sum2State;
+    Params p;
+    float clip, omb2, bc1, bc2, inv_scale;
+    __device__ explicit LambMpStage1Op(const Params& q) : p(q), omb2(fsub(1.f, q.beta2)), bc1(1.f), bc2(1.f) {
+        const float gn = __ldg(q.global_grad_norm), mx = __ldg(q.max_grad_norm);
+        clip = gn > mx ? fdiv(gn, mx) : 1.0f;
+        inv_scale = __ldg(q.inv_scale);
+        if (q.bias_correction == 1) {  // :64-70 (the reference uses a fast-math float pow; double here and in the oracle)
+            const int step = __ldg(q.step);
+            bc1 = (float)(1.0 - pow((double)q.beta1, (double)step));
+            bc2 = (float)(1.0 - pow((double)q.beta2, (double)step));
+        }
+    }
+    __device__ __forceinline__ void init(State& s) const { s.sp = 0.f; s.su = 0.f; }
+    __device__ __forceinline__ bool load(int d) const { return d != 1 || p.decay != 0.f || p.need_norms; }
+    __device__ __forceinline__ void elem(float (&x)[4], State& s) const {
+        const float w_in = x[1];
+        s.sp = fadd(s.sp, fmul(w_in, w_in));
+        const float w = p.decay == 0.f ? 0.f : w_in;
+        float m = x[2], v = x[3];
+        float sg = fdiv(fmul(x[0], inv_scale), clip);
+        if (p.mode == 0) sg = fadd(sg, fmul(p.decay, w));
+        m = fadd(fmul(m, p.beta1), fmul(p.beta3, sg));
+        v = fadd(fmul(v, p.beta2), fmul(fmul(omb2, sg), sg));
+        const float denom = fadd(fsqrt(fdiv(v, bc2)), p.eps);
+        float u = fdiv(fdiv(m, bc1), denom);
+        if (p.mode != 0) u = fadd(u, fmul(p.decay, w));
+        const float ur = Elem<Tg>::round(u);
+        s.su = fadd(s.su, fmul(ur, ur));
+        x[0] = u; x[2] = m; x[3] = v;
+    }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t*) const {
+        if (p.need_norms) {
+            const float tp = block_sum<THREADS>(s.sp, smem);
+            const float tu = block_sum<THREADS>(s.su, smem);
+            if (threadIdx.x == 0) { p.partials[tile] = tp; p.partials[p.ntiles + tile] = tu; }
+        }
+        s.sp = 0.f; s.su = 0.f;
+    }
+};
+
+// lists: u (Tg), p (Tp) [, m, v untouched, p_model (Tg)]: with kCopy the op walks the caller's 5-list table and simply
+// leaves lists 2 and 3 alone, so no second table is needed.
+template <class Tg, class Tp, bool kCopy> struct LambMpStage2Op : OpBase {
+    static constexpr int kLists = kCopy ? 5 : 2;
+    template <int D> using T = typename Types<Tg, Tp, Tp, Tp, Tg>::template at<D>;
+    static constexpr unsigned kRead = 0b00011, kWrite = kCopy ? 0b10010 : 0b00010;
+    static constexpr bool kEarlyExit = true;
+    struct Params { const float *param_norm, *update_norm, *lr; float decay; int use_nvlamb; };
+    Params p;
+    float lr, ratio;
+    __device__ explicit LambMpStage2Op(const Params& q) : p(q), lr(__ldg(q.lr)), ratio(0.f) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        ratio = lr;
+        if (p.use_nvlamb || p.decay != 0.0f) {
+            const float pn = p.param_norm[t], un = p.update_norm[t];
+            ratio = (un != 0.0f && pn != 0.0f) ? fmul(lr, fdiv(pn, un)) : lr;
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[kLists], State&) const {
+        const float w = fsub(x[1], fmul(ratio, x[0]));
+        x[1] = w;
+        if constexpr (kCopy) x[4] = Elem<Tp>::round(w);  // r_out_p = r_p: cast from the stored param_t value (:319-321)
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// AdagradFunctor: csrc/multi_tensor_adagrad.cu:63-72.   lists: g, p, h (one dtype, fp32 math)
+template <class Tp> struct AdagradOp : OpBase {
+    static constexpr int kLists = 3;
+    template <int D> using T = Tp;
+    static constexpr unsigned kRead = 0b111, kWrite = 0b110;
+    struct Params { float eps, lr, decay; int mode; };
+    Params p;
+    __device__ explicit AdagradOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void elem(float (&x)[3], State&) const {
+        float g = x[0], w = x[1], h = x[2];
+        if (p.mode == 0) {  // L2
+            g = fadd(g, fmul(p.decay, w));
+            h = fadd(h, fmul(g, g));
+            w = fsub(w, fmul(p.lr, fdiv(g, fadd(fsqrt(h), p.eps))));
+        } else {  // AdamW-style
+            h = fadd(h, fmul(g, g));
+            w = fsub(w, fmul(p.lr, fadd(fdiv(g, fadd(fsqrt(h), p.eps)), fmul(p.decay, w))));
+        }
+        x[1] = w; x[2] = h;
+    }
+};
+
+// NovoGradFunctor: csrc/multi_tensor_novograd.cu:90-107.   lists: g, p, m; per-tensor second moment (a norm) on device
+template <class Tp> struct NovoGradOp : OpBase {
+    static constexpr int kLists = 3;
+    template <int D> using T = Tp;
+    static constexpr unsigned kRead = 0b111, kWrite = 0b110;
+    struct Params { float beta1, beta2, beta3, bc1, bc2, eps, lr, decay; int mode; const float* grad_norm; };
+    Params p;
+    float gn;
+    __device__ explicit NovoGradOp(const Params& q) : p(q), gn(0.f) {}
+    __device__ __forceinline__ void begin_tensor(int t) { gn = p.grad_norm[t]; }  // written by the previous kernel
+    __device__ __forceinline__ void elem(float (&x)[3], State&) const {
+        float g = x[0], w = x[1], m = x[2];
+        const float denom = fadd(fdiv(gn, p.bc2), p.eps);
+        if (p.mode == 0) {
+            g = fadd(fdiv(g, denom), fmul(p.decay, w));
+            m = fadd(fmul(p.beta1, m), fmul(p.beta3, g));
+            w = fsub(w, fmul(p.lr, fdiv(m, p.bc1)));
+        } else {
+            m = fadd(fmul(p.beta1, m), fmul(p.beta3, g));
+            const float upd = fadd(fdiv(fdiv(m, p.bc1), denom), fmul(p.decay, w));
+            w = fsub(w, fmul(p.lr, upd));
+        }
+        x[1] = w; x[2] = m;
+    }
+};
+
+// MaxNormFunctor: csrc/multi_tensor_l2norm_kernel.cu:113-195 -- per-chunk max |x| (for NovoGrad's L-inf norm).
+struct MaxState { float mx; };
+template <int THREADS> __device__ __forceinline__ float block_max(float v, float* smem) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    float r = 0.f;
+    if (warp == 0) {
+        r = lane < THREADS / 32 ? smem[lane] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) r = fmaxf(r, __shfl_xor_sync(0xffffffffu, r, o));
+    }
+    return r;
+}
+template <class Tx> struct MaxNormOp : OpBase {
+    static constexpr int kLists = 1;
+    template <int D> using T = Tx;
+    static constexpr unsigned kRead = 0b1, kWrite = 0b0;
+    struct Params { float* partials; };
+    using State = MaxState;
+    Params p;
+    __device__ explicit MaxNormOp(const Params& q) : p(q) {}
+    __device__ __forceinline__ void init(State& s) const { s.mx = 0.f; }
+    __device__ __forceinline__ void elem(float (&x)[1], State& s) const { s.mx = fmaxf(fabsf(s.mx), fabsf(x[0])); }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+        const float tot = block_max<THREADS>(s.mx, smem);
+        if (threadIdx.x == 0) {
+            p.partials[tile] = tot;
+            if (!finite_f(tot)) *noop = 1;  // :187-188
+        }
+        s.mx = 0.f;
+    }
+};
+
+// LARSFunctor: csrc/multi_tensor_lars.cu:58-139.   lists: g, w, mom [, fp16 model copy]
+template <class Tg, class Tw, bool kCopy> struct LarsOp : OpBase {
+    static constexpr int kLists = kCopy ? 4 : 3;
+    template <int D> using T = typename Types<Tg, Tw, Tw, __half>::template at<D>;
+    static constexpr unsigned kRead = 0b0111, kWrite = kCopy ? 0b1110 : 0b0110;
+    static constexpr bool kEarlyExit = true;
+    struct Params {
+        const float *grad_norms, *param_norms;
+        float lr, trust_coefficient, eps, weight_decay, momentum;
+        int nesterov, is_skipped;
+    };
+    Params p;
+    float scaled_lr;
+    __device__ explicit LarsOp(const Params& q) : p(q), scaled_lr(q.lr) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        scaled_lr = p.lr;
+        if (!p.is_skipped) {
+            const float pn = p.param_norms[t], gn = p.grad_norms[t];
+            float trust = 1.0f;
+            if (gn > 0.0f && pn > 0.0f)
+                trust = fdiv(fmul(p.trust_coefficient, pn), fadd(fadd(gn, fmul(pn, p.weight_decay)), p.eps));
+            scaled_lr = fmul(p.lr, trust);
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[kLists], State&) const {
+        const float g = fadd(x[0], fmul(p.weight_decay, x[1]));
+        float w = x[1];
+        const float mom = fsub(fmul(x[2], p.momentum), fmul(scaled_lr, g));
+        if (p.nesterov) w = fadd(w, fsub(fmul(mom, p.momentum), fmul(scaled_lr, g)));
+        else w = fadd(w, mom);
+        x[1] = w; x[2] = mom;
+        if constexpr (kCopy) x[3] = Elem<Tw>::round(w);
+    }
 };
 
 // ------------------------------------------------------------------------------------------------

@@ -113,6 +113,43 @@ int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const MtTensorLists
                          int grad_averaging, int mode, const float* global_grad_norm, float max_grad_norm,
                          int use_nvlamb, void* scratch, size_t scratch_bytes, void* stream);
 
+/* "_mp" (mixed-precision, capturable) variants: the l2norm that does nothing once the flag is set, and LAMB with the
+ * learning rate, step, max grad norm and inverse loss scale read from DEVICE memory.  lamb_mp lists: [g, p, m, v] (one
+ * dtype) or [g, p32, m32, v32, p_model] (fp32 masters + a model copy in g's dtype).  g is multiplied by *inv_scale,
+ * overwritten with the update.  All kernels return at once when *noop_flag != 0.  scratch: mt_lamb_scratch_bytes().
+ * Replace multi_tensor_l2norm_mp_cuda (/root/reference/csrc/multi_tensor_l2norm_kernel_mp.cu:153-216) and
+ * multi_tensor_lamb_mp_cuda (/root/reference/csrc/multi_tensor_lamb_mp.cu:367-496). */
+int mt_multi_tensor_l2norm_mp(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor, float* ret,
+                              float* ret_per_tensor, void* scratch, size_t scratch_bytes, void* stream);
+int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, const float* lr, float beta1,
+                            float beta2, float epsilon, const int32_t* step, int bias_correction, float weight_decay,
+                            int grad_averaging, int mode, const float* global_grad_norm, const float* max_grad_norm,
+                            int use_nvlamb, const float* found_inf, const float* inv_scale, void* scratch,
+                            size_t scratch_bytes, void* stream);
+
+/* Adagrad (mode 0: L2, mode 1: decoupled weight decay).  Lists: [g, p, h], one dtype (f32/f16/bf16/f64), fp32 math.
+ * Replaces multi_tensor_adagrad_cuda, /root/reference/csrc/multi_tensor_adagrad.cu:84-100. */
+int mt_multi_tensor_adagrad(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float lr, float epsilon,
+                            int mode, float weight_decay, void* stream);
+
+/* NovoGrad.  Lists: [g, p, m], one dtype.  grad_norms: DEVICE float[ntensors], the running per-tensor second moment;
+ * it is first blended with this step's gradient norm (norm_type 0: L-inf, a*old + b*max|g|; otherwise L2,
+ * sqrt(a*old^2 + b*sum g^2), a = beta2, b = 1 - beta2), then used by the update.  scratch: mt_norm_scratch_bytes().
+ * Replaces multi_tensor_novograd_cuda + multi_tensor_norm_out_cuda + cleanup_v2,
+ * /root/reference/csrc/multi_tensor_novograd.cu:127-188, multi_tensor_l2norm_kernel.cu:239-299,367-456. */
+int mt_multi_tensor_novograd(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float* grad_norms, float lr,
+                             float beta1, float beta2, float epsilon, int step, int bias_correction, float weight_decay,
+                             int grad_averaging, int moment_mode, int norm_type, void* scratch, size_t scratch_bytes,
+                             void* stream);
+
+/* LARS.  Lists: [g, w, mom] or [g, w, mom, w_fp16]; grad_norms / param_norms: DEVICE float[ntensors].  Does nothing when
+ * *noop_flag != 0.  dampening, first_run, wd_after_momentum and scale are accepted and ignored, as in the reference.
+ * Replaces multi_tensor_lars_cuda, /root/reference/csrc/multi_tensor_lars.cu:141-354. */
+int mt_multi_tensor_lars(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, const float* grad_norms,
+                         const float* param_norms, float lr, float trust_coefficient, float epsilon, float weight_decay,
+                         float momentum, float dampening, int nesterov, int first_run, int wd_after_momentum, float scale,
+                         int is_skipped, void* stream);
+
 /* Legacy split LAMB.  stage1 lists: [g, p, m, v, update]; per_tensor_decay is a DEVICE float[ntensors];
  * clipped_global_grad_norm is passed by value (the reference reads the norm on the host,
  * csrc/multi_tensor_lamb_stage_1.cu:126-127).  Arithmetic is carried out in the parameter dtype.

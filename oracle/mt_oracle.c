@@ -468,6 +468,149 @@ void orc_lamb(void* const* gs, void* const* ps, void* const* ms, void* const* vs
     free(pn); free(un);
 }
 
+/* ---------------------------------------------------------------- "_mp" LAMB (csrc/multi_tensor_lamb_mp.cu) */
+
+/* LAMBStage1Functor<T,param_t>: csrc/multi_tensor_lamb_mp.cu:58-75,118-151.  g (g_dt) is multiplied by inv_scale;
+ * p, m, v are p_dt; the update is written over g in g_dt.  The reference evaluates 1 - pow(beta, step) in-kernel
+ * with a fast-math float pow; oracle and product use double pow rounded to float. */
+void orc_lamb_mp_stage1(void* g, int g_dt, const void* p, void* m, void* v, int p_dt, int64_t n,
+                        float beta1, float beta2, float beta3, int step, int bias_correction, float eps, int mode,
+                        float decay, float global_grad_norm, float max_global_grad_norm, float inv_scale) {
+    const float clip = global_grad_norm > max_global_grad_norm ? global_grad_norm / max_global_grad_norm : 1.0f;
+    float bc1 = 1.0f, bc2 = 1.0f;
+    if (bias_correction == 1) {
+        bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+        bc2 = (float)(1.0 - pow((double)beta2, (double)step));
+    }
+    const float omb2 = 1 - beta2;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float rg = ld(g, g_dt, i) * inv_scale, rm = ld(m, p_dt, i), rv = ld(v, p_dt, i);
+        float rp = (decay == 0) ? 0.f : ld(p, p_dt, i);
+        float sg = rg / clip;
+        if (mode == 0) { float dp = decay * rp; sg = sg + dp; }
+        float t1 = rm * beta1, t2 = beta3 * sg;
+        rm = t1 + t2;
+        float t3 = rv * beta2, t4 = omb2 * sg; t4 = t4 * sg;
+        rv = t3 + t4;
+        float mu = rm / bc1, vu = rv / bc2;
+        float denom = sqrtf(vu) + eps;
+        float q = mu / denom;
+        float u;
+        if (mode == 0) u = q; else { float dp = decay * rp; u = q + dp; }
+        st(g, g_dt, i, u); st(m, p_dt, i, rm); st(v, p_dt, i, rv);
+    }
+}
+
+/* LAMBStage2Functor<T,N,param_t>: csrc/multi_tensor_lamb_mp.cu:258-266,316-323. out (g_dt, may be NULL) = stored p. */
+void orc_lamb_mp_stage2(const void* u, int g_dt, void* p, int p_dt, void* out, int64_t n, float lr, float decay,
+                        int use_nvlamb, float param_norm, float update_norm) {
+    float ratio = lr;
+    if (use_nvlamb || decay != 0.0f)
+        ratio = (update_norm != 0.0f && param_norm != 0.0f) ? lr * (param_norm / update_norm) : lr;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float ru = ratio * ld(u, g_dt, i);
+        st(p, p_dt, i, ld(p, p_dt, i) - ru);
+        if (out) st(out, g_dt, i, ld(p, p_dt, i));
+    }
+}
+
+/* ---------------------------------------------------------------- Adagrad / NovoGrad / LARS */
+
+/* AdagradFunctor: csrc/multi_tensor_adagrad.cu:63-72. */
+void orc_adagrad(const void* g, void* p, void* h, int dt, int64_t n, float lr, float eps, int mode, float decay) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float rg = ld(g, dt, i), rp = ld(p, dt, i), rh = ld(h, dt, i);
+        if (mode == 0) {
+            float t = decay * rp; rg = rg + t;
+            float sq = rg * rg; rh = rh + sq;
+            float den = sqrtf(rh) + eps; float q = rg / den; float lq = lr * q;
+            rp = rp - lq;
+        } else {
+            float sq = rg * rg; rh = rh + sq;
+            float den = sqrtf(rh) + eps; float q = rg / den; float t = decay * rp; float u = q + t; float lu = lr * u;
+            rp = rp - lu;
+        }
+        st(p, dt, i, rp); st(h, dt, i, rh);
+    }
+}
+
+/* Per-tensor norm blend of multi_tensor_norm_out_cuda: csrc/multi_tensor_l2norm_kernel.cu:367-456 (host), :113-195
+ * (MaxNormFunctor), :272-298 (cleanup_v2).  Chunk partials are max|x| or sum x^2 (plain sequential fp32 here; the
+ * product's reduction order differs, tolerance 1e-5).  Returns the flag (non-finite chunk partial). */
+int orc_norm_blend(const void* x, int dt, int64_t n, int chunk_size, float* out, int norm_type, float alpha, float beta) {
+    int flag = 0;
+    float acc = 0.f;
+    for (int64_t c = 0; c < n; c += chunk_size) {
+        int64_t e = c + chunk_size < n ? c + chunk_size : n;
+        float part = 0.f;
+        if (norm_type == 0) { for (int64_t i = c; i < e; i++) part = fmaxf(fabsf(part), fabsf(ld(x, dt, i))); }
+        else { double d = 0; for (int64_t i = c; i < e; i++) { float xv = ld(x, dt, i); d += (double)(xv * xv); } part = (float)d; }
+        if (!isfinite(part)) flag = 1;
+        if (norm_type == 0) acc = fmaxf(fabsf(acc), fabsf(part)); else acc = acc + part;
+    }
+    if (norm_type == 0) { float a = alpha * (*out), b = beta * acc; *out = a + b; }
+    else { float a = alpha * (*out); a = a * (*out); float b = beta * acc; *out = sqrtf(a + b); }
+    return flag;
+}
+
+/* NovoGradFunctor: csrc/multi_tensor_novograd.cu:90-107; host part :145-156 (bc2 = sqrt(1 - beta2^step)). */
+void orc_novograd(const void* g, void* p, void* m, int dt, int64_t n, float grad_norm, float lr, float beta1, float beta2,
+                  float eps, int step, int bias_correction, float decay, int grad_averaging, int mode) {
+    float bc1 = 1.0f, bc2 = 1.0f;
+    if (bias_correction == 1) {
+        bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+        bc2 = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    }
+    (void)beta2;
+    float beta3 = 1; if (grad_averaging == 1) beta3 = 1 - beta1;
+    const float denom = grad_norm / bc2 + eps;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float rg = ld(g, dt, i), rp = ld(p, dt, i), rm = ld(m, dt, i);
+        if (mode == 0) {
+            float q = rg / denom, t = decay * rp; rg = q + t;
+            float a = beta1 * rm, b = beta3 * rg; rm = a + b;
+            float mu = rm / bc1; float lm = lr * mu;
+            rp = rp - lm;
+        } else {
+            float a = beta1 * rm, b = beta3 * rg; rm = a + b;
+            float mu = rm / bc1; float q = mu / denom, t = decay * rp; float u = q + t; float lu = lr * u;
+            rp = rp - lu;
+        }
+        st(p, dt, i, rp); st(m, dt, i, rm);
+    }
+}
+
+/* LARSFunctor: csrc/multi_tensor_lars.cu:84-135.  model_out (fp16, may be NULL) is cast from the stored weight. */
+void orc_lars(const void* g, int g_dt, void* w, int w_dt, void* mom, void* model_out, int64_t n, float grad_norm,
+              float param_norm, float lr, float trust_coefficient, float eps, float weight_decay, float momentum,
+              int nesterov, int is_skipped, const int* noop) {
+    if (noop && *noop) return;
+    float scaled_lr = lr;
+    if (!is_skipped) {
+        float trust = 1.0f;
+        if (grad_norm > 0.0f && param_norm > 0.0f) {
+            float num = trust_coefficient * param_norm; float pw = param_norm * weight_decay;
+            float den = grad_norm + pw; den = den + eps; trust = num / den;
+        }
+        scaled_lr = lr * trust;
+    }
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float ig = ld(g, g_dt, i), iw = ld(w, w_dt, i), im = ld(mom, w_dt, i);
+        float t = weight_decay * iw; ig = ig + t;
+        float a = im * momentum, b = scaled_lr * ig; im = a - b;
+        if (nesterov) { float a2 = im * momentum, b2 = scaled_lr * ig; float d = a2 - b2; iw = iw + d; }
+        else iw = iw + im;
+        st(w, w_dt, i, iw);
+        if (model_out) st(model_out, DT_F16, i, ld(w, w_dt, i));
+        st(mom, w_dt, i, im);
+    }
+}
+
 /* ---------------------------------------------------------------- legacy split LAMB (math carried out in T) */
 
 /* LAMBStage1Functor<GRAD_T,T,UPD_T>: csrc/multi_tensor_lamb_stage_1.cu:81-100; host part :126-130

@@ -161,6 +161,89 @@ def multi_tensor_lamb(chunk_size, noop_flag, tensor_lists, lr, beta1, beta2, eps
         return pn, un
 
 
+def multi_tensor_l2norm_mp(chunk_size, noop_flag, tensor_lists, per_tensor=False):
+    """csrc/multi_tensor_l2norm_kernel_mp.cu: as multi_tensor_l2norm, but nothing is computed once the flag is set
+    (the reference then returns uninitialised tensors; None here)."""
+    if int(noop_flag.item()) != 0:
+        return None, None
+    ret, rpt = multi_tensor_l2norm(chunk_size, noop_flag, tensor_lists, per_tensor)
+    if int(noop_flag.item()) != 0:   # cleanup also returns early when the main pass raised the flag (:121-123)
+        return None, None
+    return ret, rpt
+
+
+def multi_tensor_lamb_mp(chunk_size, noop_flag, tensor_lists, lr, beta1, beta2, eps, step, bias_correction, weight_decay,
+                         grad_averaging, mode, global_grad_norm, max_grad_norm, use_nvlamb, found_inf, inv_scale):
+    """csrc/multi_tensor_lamb_mp.cu:367-496.  lr / step / norms / inv_scale are 1-element tensors."""
+    depth = len(tensor_lists)
+    assert depth in (4, 5)
+    _check_lists(tensor_lists, depth)
+    if int(noop_flag.item()) != 0:
+        return
+    L = lib()
+    gs, ps, ms, vs = tensor_lists[:4]
+    outs = tensor_lists[4] if depth == 5 else [None] * len(gs)
+    g_dt, p_dt = DT[gs[0].dtype], DT[ps[0].dtype]
+    beta3 = C.c_float(1.0 - C.c_float(beta1).value).value if grad_averaging == 1 else 1.0
+    pn, _ = None, None
+    _, pnorm = _l2norm(chunk_size, noop_flag, ps, True)
+    if int(noop_flag.item()) != 0:
+        return
+    for g, p, m, v in zip(gs, ps, ms, vs):
+        L.orc_lamb_mp_stage1(_p(g), g_dt, _p(p), _p(m), _p(v), p_dt, C.c_int64(g.numel()), _f(beta1), _f(beta2), _f(beta3),
+                             C.c_int(int(step)), C.c_int(bias_correction), _f(eps), C.c_int(mode), _f(weight_decay),
+                             _f(float(global_grad_norm)), _f(float(max_grad_norm)), _f(float(inv_scale)))
+    _, unorm = _l2norm(chunk_size, noop_flag, gs, True)
+    if int(noop_flag.item()) != 0:
+        return
+    for i, (g, p, o) in enumerate(zip(gs, ps, outs)):
+        L.orc_lamb_mp_stage2(_p(g), g_dt, _p(p), p_dt, _p(o), C.c_int64(g.numel()), _f(float(lr)), _f(weight_decay),
+                             C.c_int(bool(use_nvlamb)), _f(pnorm[i]), _f(unorm[i]))
+    return pnorm, unorm
+
+
+def multi_tensor_adagrad(chunk_size, noop_flag, tensor_lists, lr, epsilon, mode, weight_decay):
+    _check_lists(tensor_lists, 3)
+    L = lib()
+    for g, p, h in zip(*tensor_lists):
+        L.orc_adagrad(_p(g), _p(p), _p(h), DT[g.dtype], C.c_int64(g.numel()), _f(lr), _f(epsilon), C.c_int(mode),
+                      _f(weight_decay))
+
+
+def multi_tensor_novograd(chunk_size, noop_flag, tensor_lists, grad_norms, lr, beta1, beta2, epsilon, step,
+                          bias_correction, weight_decay, grad_averaging, mode, norm_type):
+    """grad_norms: float32 CPU tensor [ntensors], blended in place then used."""
+    _check_lists(tensor_lists, 3)
+    L = lib()
+    L.orc_norm_blend.restype = C.c_int
+    one_minus = C.c_float(1.0 - C.c_float(beta2).value).value
+    for i, (g, p, m) in enumerate(zip(*tensor_lists)):
+        out = (C.c_float * 1)(float(grad_norms[i]))
+        if L.orc_norm_blend(_p(g), DT[g.dtype], C.c_int64(g.numel()), C.c_int(chunk_size), out, C.c_int(norm_type),
+                            _f(beta2), _f(one_minus)):
+            noop_flag.fill_(1)
+        grad_norms[i] = out[0]
+    for i, (g, p, m) in enumerate(zip(*tensor_lists)):
+        L.orc_novograd(_p(g), _p(p), _p(m), DT[g.dtype], C.c_int64(g.numel()), _f(grad_norms[i]), _f(lr), _f(beta1),
+                       _f(beta2), _f(epsilon), C.c_int(step), C.c_int(bias_correction), _f(weight_decay),
+                       C.c_int(grad_averaging), C.c_int(mode))
+
+
+def multi_tensor_lars(chunk_size, noop_flag, tensor_lists, grad_norms, param_norms, lr, trust_coefficient, epsilon,
+                      weight_decay, momentum, dampening, nesterov, first_run, wd_after_momentum, scale, is_skipped):
+    depth = len(tensor_lists)
+    assert depth in (3, 4)
+    _check_lists(tensor_lists, depth)
+    L = lib()
+    noop = (C.c_int * 1)(int(noop_flag.item()))
+    for i in range(len(tensor_lists[0])):
+        g, w, mom = tensor_lists[0][i], tensor_lists[1][i], tensor_lists[2][i]
+        out = tensor_lists[3][i] if depth == 4 else None
+        L.orc_lars(_p(g), DT[g.dtype], _p(w), DT[w.dtype], _p(mom), _p(out), C.c_int64(g.numel()), _f(grad_norms[i]),
+                   _f(param_norms[i]), _f(lr), _f(trust_coefficient), _f(epsilon), _f(weight_decay), _f(momentum),
+                   C.c_int(bool(nesterov)), C.c_int(bool(is_skipped)), noop)
+
+
 def multi_tensor_lamb_stage1_cuda(chunk_size, noop_flag, tensor_lists, per_tensor_decay, step, beta1, beta2, eps,
                                   global_grad_norm, max_global_grad_norm):
     _check_lists(tensor_lists, 5)

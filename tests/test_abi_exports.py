@@ -21,7 +21,7 @@ def test_header_symbols_are_exported():
 
     L = _lib.lib()
     syms = declared_symbols()
-    assert len(syms) >= 17
+    assert len(syms) >= 24
     for s in syms:
         assert hasattr(L, s), f"libmt_b200.so does not export {s}"
     assert set(syms) == set(_lib.EXPORTS), set(syms) ^ set(_lib.EXPORTS)
@@ -62,7 +62,9 @@ def test_amp_C_exports_reference_names():
     m = beforeholiday_b200.load_amp_C()
     for name in ("multi_tensor_scale", "multi_tensor_sgd", "multi_tensor_axpby", "multi_tensor_l2norm",
                  "multi_tensor_l2norm_scale", "multi_tensor_lamb_stage1_cuda", "multi_tensor_lamb_stage2_cuda",
-                 "multi_tensor_adam", "multi_tensor_lamb", "multi_tensor_fused_adam"):
+                 "multi_tensor_adam", "multi_tensor_lamb", "multi_tensor_fused_adam", "multi_tensor_l2norm_mp",
+                 "multi_tensor_lamb_mp", "multi_tensor_adagrad", "multi_tensor_novograd", "multi_tensor_lars",
+                 "multi_tensor_fused_adam_p2p"):
         assert callable(getattr(m, name)), name
 
 
