@@ -61,8 +61,13 @@ extern "C" int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const Mt
     if (rc) return rc;
 #define MT_ADAM(CT)                                                                                       \
     {                                                                                                     \
-        using Op = AdamOp<CT>;                                                                            \
-        typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay, mode};                 \
+        if (mode == 0) {                                                                                  \
+            using Op = AdamOp<CT, 0>;                                                                     \
+            typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay};                   \
+            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+        }                                                                                                 \
+        using Op = AdamOp<CT, 1>;                                                                         \
+        typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay};                       \
         return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
     }
     switch (tl->dtype[0]) {
@@ -175,10 +180,17 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
     const int need_norms = (use_nvlamb || weight_decay != 0.0f) ? 1 : 0;
 
     MT_DISPATCH_FHB(tl->dtype[0], Tp, "multi_tensor_lamb", {
-        using Op1 = LambStage1Op<Tp>;
-        typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
-                                global_grad_norm, partials, tb.ntiles, mode, need_norms};
-        rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+        if (mode == 0) {
+            using Op1 = LambStage1Op<Tp, 0>;
+            typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
+                                    global_grad_norm, partials, tb.ntiles, mode, need_norms};
+            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+        } else {
+            using Op1 = LambStage1Op<Tp, 1>;
+            typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
+                                    global_grad_norm, partials, tb.ntiles, mode, need_norms};
+            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+        }
         if (rc) return rc;
         if (need_norms) {
             rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream);
@@ -223,10 +235,17 @@ extern "C" int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const
     const int need_norms = (use_nvlamb || weight_decay != 0.0f) ? 1 : 0;
 #define MT_LAMB_MP(TG, TP, COPY)                                                                                    \
     {                                                                                                               \
-        using Op1 = LambMpStage1Op<TG, TP>;                                                                         \
-        typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm, max_grad_norm,  \
-                                inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms};                 \
-        rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);         \
+        if (mode == 0) {                                                                                            \
+            using Op1 = LambMpStage1Op<TG, TP, 0>;                                                                  \
+            typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
+                                    max_grad_norm, inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms}; \
+            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);     \
+        } else {                                                                                                    \
+            using Op1 = LambMpStage1Op<TG, TP, 1>;                                                                  \
+            typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
+                                    max_grad_norm, inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms}; \
+            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);     \
+        }                                                                                                           \
         if (rc) return rc;                                                                                          \
         if (need_norms) {                                                                                           \
             rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream, noop_flag);              \

@@ -53,17 +53,19 @@ template <class Tx, class Ty, class To> struct AxpbyOp : OpBase {
 
 // ------------------------------------------------------------------------------------------------
 // AdamFunctor: csrc/multi_tensor_adam.cu:94-112.   lists: g, p, m, v (one dtype, fp32 math)
-template <class Tp> struct AdamOp : OpBase {
+// kMode is a template parameter (0 = L2, 1 = AdamW) so that only one branch is compiled in: with both in one kernel
+// the 64-register budget of 4 CTAs/SM spilled.
+template <class Tp, int kMode> struct AdamOp : OpBase {
     static constexpr int kLists = 4;
     template <int D> using T = Tp;
     static constexpr unsigned kRead = 0b1111, kWrite = 0b1110;
-    struct Params { float beta1, beta2, bc1, bc2, eps, lr, decay; int mode; };
+    struct Params { float beta1, beta2, bc1, bc2, eps, lr, decay; };
     Params p;
     float omb1, omb2;
     __device__ explicit AdamOp(const Params& q) : p(q), omb1(fsub(1.f, q.beta1)), omb2(fsub(1.f, q.beta2)) {}
     __device__ __forceinline__ void elem(float (&x)[4], State&) const {
         float g = x[0], w = x[1], m = x[2], v = x[3];
-        if (p.mode == 0) {  // L2
+        if constexpr (kMode == 0) {  // L2
             g = fadd(g, fmul(p.decay, w));
             m = fadd(fmul(p.beta1, m), fmul(omb1, g));
             v = fadd(fmul(p.beta2, v), fmul(fmul(omb2, g), g));
@@ -347,7 +349,7 @@ template <class Tin, class Tout> struct L2NormScaleOp : OpBase {
 // partial sums of p^2 and (T-rounded u)^2 are written to scratch and reduced per tensor by
 // lamb_norm_finalize_kernel.   lists: g (overwritten with u), p, m, v
 struct Sum2State { float sp, su; };
-template <class Tp> struct LambStage1Op : OpBase {
+template <class Tp, int kMode> struct LambStage1Op : OpBase {
     static constexpr int kLists = 4;
     template <int D> using T = Tp;
     static constexpr unsigned kRead = 0b1111, kWrite = 0b1101;
@@ -374,12 +376,12 @@ template <class Tp> struct LambStage1Op : OpBase {
         const float w = p.decay == 0.f ? 0.f : w_in;  // r_p = 0 when decay == 0 (:123-128)
         float m = x[2], v = x[3];
         float sg = fdiv(x[0], clip);
-        if (p.mode == 0) sg = fadd(sg, fmul(p.decay, w));
+        if constexpr (kMode == 0) sg = fadd(sg, fmul(p.decay, w));
         m = fadd(fmul(m, p.beta1), fmul(p.beta3, sg));
         v = fadd(fmul(v, p.beta2), fmul(fmul(omb2, sg), sg));
         const float denom = fadd(fsqrt(fdiv(v, p.bc2)), p.eps);
         float u = fdiv(fdiv(m, p.bc1), denom);
-        if (p.mode != 0) u = fadd(u, fmul(p.decay, w));
+        if constexpr (kMode != 0) u = fadd(u, fmul(p.decay, w));
         const float ur = Elem<Tp>::round(u);  // the reference norms the STORED update
         s.su = fadd(s.su, fmul(ur, ur));
         x[0] = u; x[2] = m; x[3] = v;
@@ -418,7 +420,7 @@ template <class Tp> struct LambStage2Op : OpBase {
 // Differences from LambStage1Op: g has its own dtype Tg and is multiplied by *inv_scale first; p, m, v have dtype Tp
 // (fp32 masters or Tg); step, max_grad_norm and the learning rate are read from device memory (so a captured graph
 // replays across steps); the kernels return at once when the flag is set.
-template <class Tg, class Tp> struct LambMpStage1Op : OpBase {
+template <class Tg, class Tp, int kMode> struct LambMpStage1Op : OpBase {
     static constexpr int kLists = 4;
     template <int D> using T = typename Types<Tg, Tp, Tp, Tp>::template at<D>;
     static constexpr unsigned kRead = 0b1111, kWrite = 0b1101;
@@ -452,12 +454,12 @@ template <class Tg, class Tp> struct LambMpStage1Op : OpBase {
         const float w = p.decay == 0.f ? 0.f : w_in;
         float m = x[2], v = x[3];
         float sg = fdiv(fmul(x[0], inv_scale), clip);
-        if (p.mode == 0) sg = fadd(sg, fmul(p.decay, w));
+        if constexpr (kMode == 0) sg = fadd(sg, fmul(p.decay, w));
         m = fadd(fmul(m, p.beta1), fmul(p.beta3, sg));
         v = fadd(fmul(v, p.beta2), fmul(fmul(omb2, sg), sg));
         const float denom = fadd(fsqrt(fdiv(v, bc2)), p.eps);
         float u = fdiv(fdiv(m, bc1), denom);
-        if (p.mode != 0) u = fadd(u, fmul(p.decay, w));
+        if constexpr (kMode != 0) u = fadd(u, fmul(p.decay, w));
         const float ur = Elem<Tg>::round(u);
         s.su = fadd(s.su, fmul(ur, ur));
         x[0] = u; x[2] = m; x[3] = v;
