@@ -328,6 +328,26 @@ void multi_tensor_fused_adam(int chunk_size, at::Tensor noop_flag, TensorLists t
                                      grad_scale, step, mode, honour_noop ? 1 : 0, f.stream));
 }
 
+// Capturable form: lr, grad_scale (= loss scale, g is divided by it) and step are CUDA scalar tensors.
+void multi_tensor_fused_adam_capturable(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                        at::Tensor per_tensor_beta1, at::Tensor per_tensor_beta2,
+                                        at::Tensor per_tensor_bias_correction, at::Tensor per_tensor_eps,
+                                        at::Tensor per_tensor_weight_decay, at::Tensor lr, at::Tensor grad_scale,
+                                        at::Tensor step, int mode) {
+    Flat f;
+    flatten(tensor_lists, 4, 5, "multi_tensor_fused_adam_capturable", f);
+    TORCH_CHECK(lr.is_cuda() && lr.scalar_type() == at::kFloat && grad_scale.is_cuda() &&
+                    grad_scale.scalar_type() == at::kFloat && step.is_cuda() && step.scalar_type() == at::kInt,
+                "lr (float), grad_scale (float) and step (int32) must be CUDA tensors");
+    TORCH_CHECK(per_tensor_bias_correction.scalar_type() == at::ScalarType::Int, "per_tensor_bias_correction must be int32");
+    check(mt_multi_tensor_fused_adam_capturable(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(),
+                                                per_tensor_beta2.data_ptr<float>(),
+                                                per_tensor_bias_correction.data_ptr<int32_t>(),
+                                                per_tensor_eps.data_ptr<float>(), per_tensor_weight_decay.data_ptr<float>(),
+                                                lr.data_ptr<float>(), grad_scale.data_ptr<float>(),
+                                                step.data_ptr<int32_t>(), mode, f.stream));
+}
+
 // Fused reduce-scatter + Adam + all-gather over peer memory.  grad_ptrs / param_ptrs: every rank's flat buffer base
 // address as mapped in this process (e.g. torch.distributed._symmetric_memory handle.buffer_ptrs).
 void multi_tensor_fused_adam_p2p(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
@@ -392,6 +412,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),
           py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
           py::arg("honour_noop") = false);
+    m.def("multi_tensor_fused_adam_capturable", &multi_tensor_fused_adam_capturable,
+          "Mixed-precision Adam with device-side lr / grad_scale / step (CUDA-graph capturable)");
     m.def("multi_tensor_fused_adam_p2p", &multi_tensor_fused_adam_p2p,
           "Fused gradient reduce-scatter + sharded Adam + parameter all-gather over NVLink peer memory",
           py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor_beta1"),

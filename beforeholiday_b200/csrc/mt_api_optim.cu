@@ -81,19 +81,24 @@ extern "C" int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const Mt
 }
 
 // ---------------------------------------------------------------------------------------------------
-extern "C" int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
-                                          const float* per_tensor_beta1, const float* per_tensor_beta2,
-                                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
-                                          const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
-                                          int mode, int honour_noop, void* stream_) {
-    MT_PROLOGUE("multi_tensor_fused_adam", 4, 5)
+static int fused_adam_impl(const char* who, int32_t* noop_flag, const MtTensorLists* tl, const float* per_tensor_beta1,
+                           const float* per_tensor_beta2, const int32_t* per_tensor_bias_correction,
+                           const float* per_tensor_eps, const float* per_tensor_weight_decay, float lr, float grad_scale,
+                           int step, int mode, int honour_noop, const float* lr_dev, const float* grad_scale_dev,
+                           const int32_t* step_dev, void* stream_) {
+    using namespace mt;
+    int rc = validate_lists(tl, 4, 5, who);
+    if (rc) return rc;
+    if (!noop_flag) return set_error(MT_EINVAL, "%s: noop_flag is NULL", who);
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(tl->device);
+    if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
     if (!per_tensor_beta1 || !per_tensor_beta2 || !per_tensor_bias_correction || !per_tensor_eps || !per_tensor_weight_decay)
-        return set_error(MT_EINVAL, "multi_tensor_fused_adam: per-tensor hyper-parameter arrays must be device pointers");
+        return set_error(MT_EINVAL, "%s: per-tensor hyper-parameter arrays must be device pointers", who);
     for (int d = 0; d < 3; d++)
-        if (tl->dtype[d] != MT_F32)
-            return set_error(MT_EINVAL, "multi_tensor_fused_adam: p, m, v must be float32");
+        if (tl->dtype[d] != MT_F32) return set_error(MT_EINVAL, "%s: p, m, v must be float32", who);
     if (tl->depth == 5 && tl->dtype[4] != tl->dtype[3])
-        return set_error(MT_EINVAL, "multi_tensor_fused_adam: p_copy must have the gradient dtype");
+        return set_error(MT_EINVAL, "%s: p_copy must have the gradient dtype", who);
     DevTable tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
@@ -102,15 +107,40 @@ extern "C" int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, co
     {                                                                                                     \
         using Op = DistAdamOp<TG, COPY, HN>;                                                              \
         typename Op::Params prm{per_tensor_beta1, per_tensor_beta2, per_tensor_eps, per_tensor_weight_decay, \
-                                per_tensor_bias_correction, lr, grad_scale, step, mode};                  \
+                                per_tensor_bias_correction, lr, grad_scale, step, mode, lr_dev, grad_scale_dev, step_dev}; \
         return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
     }
-    MT_DISPATCH_FHB(tl->dtype[3], Tg, "multi_tensor_fused_adam", {
+    MT_DISPATCH_FHB(tl->dtype[3], Tg, who, {
         if (copy) { if (honour_noop) MT_DADAM(Tg, true, true) else MT_DADAM(Tg, true, false) }
         else      { if (honour_noop) MT_DADAM(Tg, false, true) else MT_DADAM(Tg, false, false) }
     })
 #undef MT_DADAM
     return MT_OK;
+}
+
+extern "C" int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                          const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                          const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                                          int mode, int honour_noop, void* stream_) {
+    (void)chunk_size;
+    return fused_adam_impl("multi_tensor_fused_adam", noop_flag, tl, per_tensor_beta1, per_tensor_beta2,
+                           per_tensor_bias_correction, per_tensor_eps, per_tensor_weight_decay, lr, grad_scale, step, mode,
+                           honour_noop, nullptr, nullptr, nullptr, stream_);
+}
+
+extern "C" int mt_multi_tensor_fused_adam_capturable(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                                     const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                                     const int32_t* per_tensor_bias_correction,
+                                                     const float* per_tensor_eps, const float* per_tensor_weight_decay,
+                                                     const float* lr, const float* grad_scale, const int32_t* step,
+                                                     int mode, void* stream_) {
+    (void)chunk_size;
+    if (!lr || !grad_scale || !step)
+        return mt::set_error(MT_EINVAL, "multi_tensor_fused_adam_capturable: lr, grad_scale, step must be device pointers");
+    return fused_adam_impl("multi_tensor_fused_adam_capturable", noop_flag, tl, per_tensor_beta1, per_tensor_beta2,
+                           per_tensor_bias_correction, per_tensor_eps, per_tensor_weight_decay, 0.f, 1.f, 0, mode, 1, lr,
+                           grad_scale, step, stream_);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -95,11 +95,20 @@ template <class Tg, bool kCopy, bool kHonourNoop> struct DistAdamOp : OpBase {
         const int32_t* bias_correction;
         float lr, grad_scale;
         int step, mode;
+        // Capturable form: when non-NULL these DEVICE scalars replace lr / grad_scale / step, so a captured CUDA graph
+        // replays correctly while the host-side values move on.
+        const float* lr_dev;
+        const float* grad_scale_dev;
+        const int32_t* step_dev;
     };
     Params p;
     float b1, b2, omb1, omb2, bc1, bc2, eps, decay;
     int bc_on;
-    __device__ explicit DistAdamOp(const Params& q) : p(q), b1(-1.f), b2(-1.f), bc1(1.f), bc2(1.f), bc_on(-1) {}
+    __device__ explicit DistAdamOp(const Params& q) : p(q), b1(-1.f), b2(-1.f), bc1(1.f), bc2(1.f), bc_on(-1) {
+        if (q.lr_dev) p.lr = __ldg(q.lr_dev);
+        if (q.grad_scale_dev) p.grad_scale = __ldg(q.grad_scale_dev);
+        if (q.step_dev) p.step = __ldg(q.step_dev);
+    }
     __device__ __forceinline__ void begin_tensor(int t) {
         const float nb1 = __ldg(p.beta1 + t), nb2 = __ldg(p.beta2 + t);
         const int on = __ldg(p.bias_correction + t) == 1;

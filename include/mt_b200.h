@@ -175,6 +175,16 @@ int mt_multi_tensor_fused_adam(int chunk_size, int32_t* noop_flag, const MtTenso
                                const float* per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
                                int honour_noop, void* stream);
 
+/* Capturable form of mt_multi_tensor_fused_adam: lr, grad_scale and step are DEVICE scalars read by the kernel, the
+ * flag is always honoured.  A step captured in a CUDA graph therefore replays correctly while a host-side schedule
+ * updates those scalars (and while the overflow check that precedes it may set the flag).  No counterpart in this
+ * fork of the reference (upstream Apex has multi_tensor_adam_capturable); same arithmetic as DistAdamFunctor. */
+int mt_multi_tensor_fused_adam_capturable(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                          const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                          const float* per_tensor_weight_decay, const float* lr,
+                                          const float* grad_scale, const int32_t* step, int mode, void* stream);
+
 /* Fused gradient reduce-scatter + sharded Adam + parameter all-gather in one kernel over NVLink peer memory.
  * Same arithmetic and lists as mt_multi_tensor_fused_adam with p_copy ([p, m, v, g, p_copy], honour_noop on), but list 3
  * is read from EVERY rank's gradient buffer (summed in rank order, rounded once to the gradient dtype) and list 4 is

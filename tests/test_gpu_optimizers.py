@@ -240,3 +240,57 @@ def test_loss_scaler_unscale_with_stashed():
     scaler.clear_overflow_state()
     scaler.unscale_with_stashed(model, stashed, master)
     assert scaler.update_scale() is True
+
+
+def test_fused_adam_master_weights_and_capturable():
+    """The 28 B/param route through the optimizer class: bf16 params + fp32 masters, loss-scaled grads, found_inf skip;
+    and the capturable variant replayed from a CUDA graph, both against torch.optim.AdamW on fp32 masters."""
+    from beforeholiday_b200.optimizers import FusedAdam
+
+    torch.manual_seed(6)
+    sizes = [70001, 333, 4096]
+    base = [torch.rand(n, device="cuda").bfloat16() for n in sizes]
+    ref_p = [torch.nn.Parameter(b.float().clone()) for b in base]
+    ref = torch.optim.AdamW(ref_p, lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+    kw = dict(lr=1e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1, master_weights=True)
+    a = [torch.nn.Parameter(b.clone()) for b in base]
+    b_ = [torch.nn.Parameter(b.clone()) for b in base]
+    oa, ob = FusedAdam(a, **kw), FusedAdam(b_, capturable=True, **kw)
+    static_g = [torch.zeros(n, device="cuda", dtype=torch.bfloat16) for n in sizes]
+    for p, g in zip(b_, static_g):
+        p.grad = g
+    inv_scale = torch.tensor([1.0 / 1024], device="cuda")
+    found = torch.zeros(1, device="cuda")
+    graph = None
+    for it in range(5):
+        grads = [(torch.rand(n, device="cuda") * 1e-2) for n in sizes]
+        overflow = it == 2
+        found.fill_(1.0 if overflow else 0.0)
+        for p, g in zip(a, grads):
+            p.grad = (g * 1024).bfloat16()
+        for s, g in zip(static_g, grads):
+            s.copy_((g * 1024).bfloat16())
+        if not overflow:
+            for p, g in zip(ref_p, grads):
+                p.grad = (g * 1024).bfloat16().float() / 1024
+            ref.step()
+        oa.step(inv_scale=inv_scale, found_inf=found)
+        if it == 1:      # capture after one eager warm-up step
+            graph = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(graph, stream=side):
+                    ob.step(inv_scale=inv_scale, found_inf=found)
+            torch.cuda.current_stream().wait_stream(side)
+        if graph is None:
+            ob.step(inv_scale=inv_scale, found_inf=found)
+        else:
+            graph.replay()
+    torch.cuda.synchronize()
+    assert int(ob.param_groups[0]["step"].item()) == 4          # the overflow step was not counted on the device
+    for r, x, y in zip(ref_p, a, b_):
+        mx, my = oa.state[x]["master_param"], ob.state[y]["master_param"]
+        assert bits_equal(mx, my) and bits_equal(x, y)           # eager == graph replay
+        assert bits_equal(x.detach(), mx.bfloat16())             # model copy is the rounded master
+        assert rel_close(mx, r, 2e-6, 2e-7)
