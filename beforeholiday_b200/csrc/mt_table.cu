@@ -6,6 +6,7 @@
 // >=1042 for 50k small tensors).  Here the table lives in device memory, is built once per distinct
 // (pointer set, sizes, tile size) and is found again by hash, so a steady-state optimizer step uploads nothing
 // and issues ONE launch per op.
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -77,6 +78,10 @@ uint64_t count_tiles(const MtTensorLists* tl, int tile_elems) {
 }
 
 int choose_tile_elems(const MtTensorLists* tl, int device) {
+    // MT_TILE_ELEMS: tuning override (multiple of 2048)
+    const char* forced_env = getenv("MT_TILE_ELEMS");
+    const int forced = forced_env ? atoi(forced_env) : 0;
+    if (forced >= kRound && forced % kRound == 0) return forced;
     DeviceInfo di;
     if (device_info(device, &di) != MT_OK || di.sms <= 0) di.sms = 148;
     // want >= 4 waves of (4 CTAs/SM) so that the tail of the last wave is small
