@@ -12,6 +12,9 @@
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
 
+#include <algorithm>
+#include <memory>
+#include <thread>
 #include <tuple>
 #include <vector>
 
@@ -55,60 +58,130 @@ struct FastSeq {
     FastSeq& operator=(const FastSeq&) = delete;
 };
 
-// Validation + flattening.  Same checks, same messages as multi_tensor_apply<depth>()
-// (/root/reference/csrc/multi_tensor_apply.cuh:53-72), but walking the Python lists directly: the reference's
-// signature (std::vector<std::vector<at::Tensor>> by value) costs a type-cast plus a reference-count round trip per
-// tensor, which at 50k tensors x 3 lists is several milliseconds -- more than the kernel itself on a B200.
+// One (list, tensor) entry: the reference's per-tensor checks (/root/reference/csrc/multi_tensor_apply.cuh:60-71).
+// Returns NULL or a static error message; never throws and never calls into Python, so it may run on worker threads.
+// *special is set for entries the fast path does not handle (tensor subclasses needing isinstance, sparse tensors).
+inline const char* check_entry(PyObject* item, const c10::Device& ref_device, at::ScalarType st0, bool first_list,
+                               int64_t* numel_slot, const void** ptr_slot, bool* special) {
+    if (!THPVariable_CheckExact(item)) { *special = true; return nullptr; }
+    const at::Tensor& x = THPVariable_Unpack(item);
+    if (x.is_sparse()) { *special = true; return nullptr; }
+    if (!x.is_contiguous() && !x.is_contiguous(at::MemoryFormat::ChannelsLast) &&
+        !x.is_contiguous(at::MemoryFormat::ChannelsLast3d))
+        return "A tensor was not contiguous.";
+    if (x.device() != ref_device) return "A tensor was not on the same device as the first tensor";
+    const int64_t n = x.numel();
+    if (first_list) *numel_slot = n;
+    else if (n != *numel_slot) return "Size mismatch";
+    if (x.scalar_type() != st0) return "all tensors of one list must share a dtype";
+    *ptr_slot = x.data_ptr();
+    return nullptr;
+}
+
+// Validation + flattening.  Same checks, same messages as multi_tensor_apply<depth>(), but walking the Python lists
+// directly: the reference's signature (std::vector<std::vector<at::Tensor>> by value) costs a type-cast plus a
+// reference-count round trip per tensor, which at 50k tensors x 3 lists is several milliseconds -- more than the
+// kernel itself on a B200.  Long lists are checked by a few worker threads (pure reads of tensor metadata).
 void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, const char* who, Flat& f) {
     FastSeq outer(lists_obj.ptr(), "tensor_lists must be a sequence of sequences of tensors");
     const size_t depth = (size_t)outer.size();
     TORCH_CHECK(depth >= depth_lo && depth <= depth_hi, "tensor_lists.size() != depth");
-    size_t len0 = 0;
-    c10::Device ref_device(c10::kCPU);
+    std::vector<std::unique_ptr<FastSeq>> inner;
+    inner.reserve(depth);
+    for (size_t l = 0; l < depth; l++)
+        inner.emplace_back(new FastSeq(outer[l], "tensor_lists must be a sequence of sequences of tensors"));
+    const size_t len0 = (size_t)inner[0]->size();
+    TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
+    for (size_t l = 0; l < depth; l++) TORCH_CHECK((size_t)inner[l]->size() == len0, "Size mismatch among tensor lists");
+    TORCH_CHECK(THPVariable_Check((*inner[0])[0]), who, ": tensor_lists must contain tensors");
+    f.first = THPVariable_Unpack((*inner[0])[0]);
+    const c10::Device ref_device = f.first.device();
+    TORCH_CHECK(ref_device.type() == at::kCUDA, "expected input to be on cuda");
+    f.ptrs.assign(depth * len0, nullptr);
+    f.numel.assign(len0, 0);
+    at::ScalarType st0[MT_MAX_DEPTH];
     for (size_t l = 0; l < depth; l++) {
-        FastSeq inner(outer[l], "tensor_lists must be a sequence of sequences of tensors");
-        const size_t len = (size_t)inner.size();
-        if (l == 0) {
-            len0 = len;
-            TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
-            TORCH_CHECK(THPVariable_Check(inner[0]), who, ": tensor_lists must contain tensors");
-            f.first = THPVariable_Unpack(inner[0]);
-            ref_device = f.first.device();
-            TORCH_CHECK(ref_device.type() == at::kCUDA, "expected input to be on cuda");
-            f.ptrs.resize(depth * len0);
-            f.numel.resize(len0);
+        PyObject* it0 = (*inner[l])[0];
+        TORCH_CHECK(THPVariable_Check(it0), who, ": tensor_lists must contain tensors");
+        st0[l] = THPVariable_Unpack(it0).scalar_type();
+        f.tl.dtype[l] = dtype_tag(st0[l], who);
+    }
+
+    // fast path over [t0, t1): list 0 first (it defines numel), then the others
+    auto run_range = [&](size_t t0, size_t t1, const char** err, bool* special) {
+        for (size_t l = 0; l < depth && !*err; l++) {
+            PyObject** items = PySequence_Fast_ITEMS(inner[l]->o);
+            for (size_t t = t0; t < t1; t++) {
+                const char* e = check_entry(items[t], ref_device, st0[l], l == 0, &f.numel[t], &f.ptrs[l * len0 + t], special);
+                if (e) { *err = e; break; }
+            }
         }
-        TORCH_CHECK(len == len0, "Size mismatch among tensor lists");
-        at::ScalarType st0 = at::ScalarType::Undefined;
-        for (size_t t = 0; t < len0; t++) {
-            PyObject* item = inner[t];
-            TORCH_CHECK(THPVariable_Check(item), who, ": tensor_lists must contain tensors");
-            const at::Tensor& x = THPVariable_Unpack(item);
-            const bool sparse = x.is_sparse();
-            bool contiguous_memory = sparse ? x._values().is_contiguous() : x.is_contiguous();
-            if (!contiguous_memory)
-                contiguous_memory = x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
-                                    x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
-            TORCH_CHECK(contiguous_memory, "A tensor was not contiguous.");
-            TORCH_CHECK(x.device() == ref_device, "A tensor was not on the same device as the first tensor");
-            const int64_t n = x.numel();
-            if (l == 0) f.numel[t] = n;
-            else TORCH_CHECK(n == f.numel[t], "Size mismatch");
-            // The reference dispatches on element [0] of each list and reinterprets the rest; a mixed list is a
-            // silent misread there.  Here it is an error.
-            if (t == 0) st0 = x.scalar_type();
-            else TORCH_CHECK(x.scalar_type() == st0, who, ": all tensors of one list must share a dtype");
-            if (sparse) {  // densify, as multi_tensor_apply.cuh:92-95
+    };
+    const char* err = nullptr;
+    bool special = false;
+    const size_t entries = depth * len0;
+    unsigned nthreads = 1;
+    if (entries >= 32768) {
+        nthreads = std::min(8u, std::max(1u, std::thread::hardware_concurrency() / 2));
+    }
+    if (nthreads <= 1) {
+        run_range(0, len0, &err, &special);
+    } else {
+        std::vector<std::thread> workers;
+        std::vector<const char*> errs(nthreads, nullptr);
+        std::vector<char> specials(nthreads, 0);
+        const size_t per = (len0 + nthreads - 1) / nthreads;
+        for (unsigned w = 0; w < nthreads; w++) {
+            const size_t t0 = std::min(len0, (size_t)w * per), t1 = std::min(len0, t0 + per);
+            workers.emplace_back([&, w, t0, t1] {
+                bool sp = false;
+                run_range(t0, t1, &errs[w], &sp);
+                specials[w] = sp;
+            });
+        }
+        for (auto& th : workers) th.join();
+        for (unsigned w = 0; w < nthreads; w++) {
+            if (errs[w] && !err) err = errs[w];
+            special = special || specials[w];
+        }
+    }
+    if (special) {
+        // slow path (rare): tensor subclasses that need isinstance(), sparse tensors (densified as
+        // multi_tensor_apply.cuh:92-95 does).  Serial, with the GIL, may allocate.
+        err = nullptr;
+        for (size_t l = 0; l < depth; l++)
+            for (size_t t = 0; t < len0; t++) {
+                PyObject* item = (*inner[l])[t];
+                TORCH_CHECK(THPVariable_Check(item), who, ": tensor_lists must contain tensors");
+                const at::Tensor& x = THPVariable_Unpack(item);
+                if (!x.is_sparse()) {
+                    bool sp2 = false;
+                    PyObject* exact = item;
+                    const char* e = THPVariable_CheckExact(exact)
+                        ? check_entry(item, ref_device, st0[l], l == 0, &f.numel[t], &f.ptrs[l * len0 + t], &sp2) : nullptr;
+                    if (!THPVariable_CheckExact(exact)) {  // subclass: same checks through the Tensor API
+                        bool cm = x.is_contiguous() || x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
+                                  x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
+                        TORCH_CHECK(cm, "A tensor was not contiguous.");
+                        TORCH_CHECK(x.device() == ref_device, "A tensor was not on the same device as the first tensor");
+                        if (l == 0) f.numel[t] = x.numel(); else TORCH_CHECK(x.numel() == f.numel[t], "Size mismatch");
+                        TORCH_CHECK(x.scalar_type() == st0[l], who, ": all tensors of one list must share a dtype");
+                        f.ptrs[l * len0 + t] = x.data_ptr();
+                    }
+                    TORCH_CHECK(!e, e);
+                    continue;
+                }
+                TORCH_CHECK(x._values().is_contiguous(), "A tensor was not contiguous.");
+                TORCH_CHECK(x.device() == ref_device, "A tensor was not on the same device as the first tensor");
+                if (l == 0) f.numel[t] = x.numel(); else TORCH_CHECK(x.numel() == f.numel[t], "Size mismatch");
+                TORCH_CHECK(x.scalar_type() == st0[l], who, ": all tensors of one list must share a dtype");
                 at::Tensor dst = at::zeros(x.sizes(), x.options().layout(at::kStrided));
                 dst.add_(x);
                 f.keep.push_back(dst);
                 f.ptrs[l * len0 + t] = dst.data_ptr();
-            } else {
-                f.ptrs[l * len0 + t] = x.data_ptr();
             }
-        }
-        f.tl.dtype[l] = dtype_tag(st0, who);
     }
+    TORCH_CHECK(!err, err);
     f.device = ref_device.index();
     f.tl.depth = (int32_t)depth;
     f.tl.device = (int32_t)f.device;

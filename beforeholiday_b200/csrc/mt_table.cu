@@ -84,10 +84,20 @@ int choose_tile_elems(const MtTensorLists* tl, int device) {
     if (forced >= kRound && forced % kRound == 0) return forced;
     DeviceInfo di;
     if (device_info(device, &di) != MT_OK || di.sms <= 0) di.sms = 148;
-    // want >= 4 waves of (4 CTAs/SM) so that the tail of the last wave is small
+    // want >= 4 waves of (4 CTAs/SM) so that the tail of the last wave is small; one pass counts the tiles for every
+    // candidate size (16384, 8192, 4096)
     const uint64_t want = (uint64_t)di.sms * 4 * 4;
-    for (int tile = kMaxTile; tile > kRound; tile >>= 1)
-        if (count_tiles(tl, tile) >= want) return tile;
+    uint64_t cnt[3] = {0, 0, 0};
+    for (int64_t t = 0; t < tl->ntensors; t++) {
+        const uint64_t n = (uint64_t)tl->numel[t];
+        cnt[0] += (n + 16383) >> 14;
+        cnt[1] += (n + 8191) >> 13;
+        cnt[2] += (n + 4095) >> 12;
+    }
+    static_assert(kMaxTile == 16384 && kRound == 2048, "candidate tile sizes are hard-wired below");
+    if (cnt[0] >= want) return 16384;
+    if (cnt[1] >= want) return 8192;
+    if (cnt[2] >= want) return 4096;
     return kRound;
 }
 
@@ -124,16 +134,26 @@ inline uint64_t mix64(uint64_t h, uint64_t v) {
 }
 
 uint64_t hash_blob(const uint8_t* p, size_t n) {
-    uint64_t h = 0x243f6a8885a308d3ull ^ n;
+    // four independent lanes: the multiply chain of one lane would make a 1.8 MB table (50k tensors) cost ~0.5 ms
+    uint64_t h[4] = {0x243f6a8885a308d3ull ^ n, 0x13198a2e03707344ull, 0xa4093822299f31d0ull, 0x082efa98ec4e6c89ull};
     size_t i = 0;
+    for (; i + 32 <= n; i += 32) {
+        uint64_t v[4];
+        memcpy(v, p + i, 32);
+        h[0] = mix64(h[0], v[0]);
+        h[1] = mix64(h[1], v[1]);
+        h[2] = mix64(h[2], v[2]);
+        h[3] = mix64(h[3], v[3]);
+    }
     for (; i + 8 <= n; i += 8) {
         uint64_t v;
         memcpy(&v, p + i, 8);
-        h = mix64(h, v);
+        h[0] = mix64(h[0], v);
     }
     uint64_t v = 0;
     if (i < n) memcpy(&v, p + i, n - i);
-    return mix64(h, v);
+    h[0] = mix64(h[0], v);
+    return mix64(mix64(h[0], h[1]), mix64(h[2], h[3]));
 }
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -170,7 +190,9 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
     const size_t bytes = off_ptrs + (size_t)depth * nt * 8;
 
     thread_local std::vector<uint8_t> blob;
-    blob.assign(bytes, 0);
+    blob.resize(bytes);
+    memset(blob.data(), 0, off_tb);  // header padding; the arrays below are fully overwritten (plus their alignment gap)
+    if (off_numel > off_tb + (nt + 1) * 4) memset(blob.data() + off_tb + (nt + 1) * 4, 0, off_numel - (off_tb + (nt + 1) * 4));
     {
         int32_t hdr[4] = {depth, tile_elems, 0, 0};
         memcpy(blob.data(), hdr, sizeof hdr);
