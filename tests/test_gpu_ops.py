@@ -184,6 +184,18 @@ def test_l2norm_flag_semantics(amp_C, oracle):
         assert bool(ng.isfinite().cpu().item()) == bool(nc.isfinite().item())
 
 
+def test_l2norm_flag_when_only_the_chunk_sum_overflows(amp_C, oracle):
+    # 65536-element chunk whose four 16384-element quarters each sum to 1.6e38 (finite) but whose total is 6.5e38:
+    # the reference's chunk partial is inf -> flag.  (One tile per reference chunk is what gives the product the same
+    # granularity; a finer tiling would miss this case.)
+    x = torch.full((65536 + 100,), 1e17)
+    (ng, _), (nc, _) = run_both(amp_C, oracle, "multi_tensor_l2norm", [[x]], (False,), chunk=65536)
+    assert torch.isinf(ng).all() and torch.isinf(nc).all()
+    y = torch.full((65536 + 100,), 0.4e17)   # chunk sum 1.0e38: finite everywhere -> no flag
+    (ng, _), (nc, _) = run_both(amp_C, oracle, "multi_tensor_l2norm", [[y]], (False,), chunk=65536)
+    assert max_rel(ng, nc) < 1e-5
+
+
 @pytest.mark.parametrize("in_t,out_t", [(F32, F32), (F16, F32), (F32, F16), (F16, F16)])
 def test_l2norm_scale(amp_C, oracle, in_t, out_t):
     lists = make_lists([in_t, out_t], [0, 5, 4097, 200001], seed=7)
