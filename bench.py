@@ -100,7 +100,7 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------ CPU arm
-def cpu_arm(sample_params: int, budget_s: float, steps_hint: int | None = None):
+def cpu_arm(sample_params: int, budget_s: float, steps_hint: int | None = None, warmup: int = 1):
     """Time the CPU oracle port (OpenMP, all threads) and torch.optim.AdamW on a bounded slice."""
     from oracle import mt_oracle as O
 
@@ -119,7 +119,8 @@ def cpu_arm(sample_params: int, budget_s: float, steps_hint: int | None = None):
         O.multi_tensor_fused_adam(8192, flag, [[p], [m], [v], [g], [pc]], [HP["beta1"]], [HP["beta2"]], [1], [HP["eps"]],
                                   [HP["wd"]], HP["lr"], HP["grad_scale"], i + 1, HP["mode"])
 
-    step(0)  # warm
+    for w in range(max(1, warmup)):  # untimed warm-up steps
+        step(w)
     t0 = time.perf_counter()
     k = 0
     times = []
@@ -128,7 +129,7 @@ def cpu_arm(sample_params: int, budget_s: float, steps_hint: int | None = None):
         step(k + 1)
         times.append(time.perf_counter() - s)
         k += 1
-        if (steps_hint and k >= steps_hint) or (time.perf_counter() - t0) > budget_s * 0.5:
+        if (steps_hint and k >= steps_hint) or (not steps_hint and (time.perf_counter() - t0) > budget_s * 0.5):
             break
     port_t = sum(times) / len(times)
 
@@ -160,7 +161,8 @@ def run_reference_arm(args, rank, world):
     if rank != 0:
         return
     sample = int(os.environ.get("MT_BENCH_CPU_SAMPLE", 256 * 1024 * 1024))
-    r = cpu_arm(sample, budget_s=max(10.0, min(120.0, 4.0 * (args.steps + args.warmup))), steps_hint=None)
+    # exactly K timed steps after W warm-up steps, each step one pass over the bounded sample (~75 ms on 16 cores)
+    r = cpu_arm(sample, budget_s=60.0, steps_hint=args.steps, warmup=args.warmup)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
