@@ -64,7 +64,7 @@ class FlatLayout:
             self.offsets.append(o)
             o += _ceil_to(n, align)
         self.total = o
-        unit = world * 1024
+        unit = world * 256   # every sub-shard starts on a 256-element (>= 512-byte) boundary
         nb = max(1, -(-self.total // max(unit, _ceil_to(bucket_cap_elems, unit))))
         self.bucket_elems = _ceil_to(-(-self.total // nb), unit)
         self.nbuckets = -(-self.total // self.bucket_elems)
@@ -112,9 +112,17 @@ class DistributedFusedAdam:
         self.rank = dist.get_rank(self.group) if dist.is_initialized() else 0
         if params is not None:
             params = list(params)
+            if params and isinstance(params[0], dict):
+                # torch-style param groups: weight_decay may differ per group (it is a per-tensor input of the kernel);
+                # lr / betas / eps are shared by the whole optimizer
+                groups, params, per_param_weight_decay = params, [], []
+                for g in groups:
+                    ps = list(g['params'])
+                    params += ps
+                    per_param_weight_decay += [g.get('weight_decay', weight_decay)] * len(ps)
             numels = [p.numel() for p in params]
+            grad_dtype = param_dtype = params[0].dtype
             device = params[0].device if device is None else device
-            param_dtype = params[0].dtype
         self.params = params
         self.device = torch.device(device if device is not None else "cuda")
         self.grad_dtype, self.param_dtype = grad_dtype, param_dtype
@@ -248,12 +256,19 @@ class DistributedFusedAdam:
 
         return load_amp_C()
 
-    def _update_bucket(self, b: int, grad_scale: float):
+    def _update_bucket(self, b: int, grad_scale):
+        """grad_scale: Python float, or a 1-element CUDA tensor (then lr / step are also passed on the device and the
+        kernel reads all three there -- no host round trip for a clipping coefficient computed on the GPU)."""
         lists, hp = self._per_bucket[b]
         if not lists[0]:
             return
-        self._amp_C().multi_tensor_fused_adam(8192, self.noop, lists, *hp, self.lr, grad_scale, self.step_count,
-                                              1 if self.adam_w_mode else 0, True)
+        mode = 1 if self.adam_w_mode else 0
+        if isinstance(grad_scale, torch.Tensor):
+            self._amp_C().multi_tensor_fused_adam_capturable(8192, self.noop, lists, *hp, self._lr_dev, grad_scale,
+                                                             self._step_dev, mode)
+        else:
+            self._amp_C().multi_tensor_fused_adam(8192, self.noop, lists, *hp, self.lr, grad_scale, self.step_count,
+                                                  mode, True)
 
     def _all_fragments_launch_set(self, wd_of=None):
         if getattr(self, "_all_set", None) is None:
@@ -301,11 +316,34 @@ class DistributedFusedAdam:
         self._all_reduce_scalar(self.noop, dist.ReduceOp.MAX)
         return sq.sqrt()
 
-    def step(self, grad_scale: float = 1.0, grads_already_reduced: bool = False):
-        """One optimizer step.  Gradients are expected in self.grads_flat (local, un-reduced unless told otherwise)."""
+    def _step_clipped(self, scale: float, max_grad_norm: float):
+        """reduce-scatter everything -> global norm of the averaged gradients (shard sums + scalar all-reduce, reference
+        :808-887) -> update with the clip factor folded into the kernel's gradient divisor (kept on the device) ->
+        all-gather.  Returns the unclipped global norm as a device tensor."""
+        L = self.layout
+        for b in range(L.nbuckets):
+            self._reduce_scatter(b)
+        norm = self.grad_norm() / scale
+        divisor = (scale * torch.clamp(norm / (max_grad_norm + 1e-6), min=1.0)).float().reshape(1)
+        if not hasattr(self, "_lr_dev"):
+            self._lr_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self._step_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._lr_dev.fill_(self.lr)
+        self._step_dev.fill_(self.step_count)
+        for b in range(L.nbuckets):
+            self._update_bucket(b, divisor)
+            self._all_gather(b)
+        return norm
+
+    def step(self, grad_scale: float = 1.0, grads_already_reduced: bool = False, max_grad_norm: Optional[float] = None):
+        """One optimizer step.  Gradients are expected in self.grads_flat (local, un-reduced unless told otherwise).
+        With max_grad_norm the averaged gradients are clipped to that global L2 norm (and the norm is returned)."""
         self.step_count += 1
         L = self.layout
         scale = grad_scale * (self.world if (self.average_grad_sync and not grads_already_reduced) else 1)
+        if max_grad_norm is not None:
+            assert not grads_already_reduced
+            return self._step_clipped(scale, float(max_grad_norm))
         if self.rs_stream is None:  # serial: single GPU, or overlap disabled
             for b in range(L.nbuckets):
                 if not grads_already_reduced:

@@ -18,7 +18,7 @@ SIZES = [1000, 7, 4096, 33333, 1, 129]
 def test_layout_partitions_flat_space_exactly():
     for world in (1, 2, 4, 8):
         lay0 = FlatLayout(SIZES, world, 0, elem_bytes=2, bucket_cap_elems=8192)
-        assert lay0.padded % (world * 1024) == 0 and lay0.padded >= lay0.total
+        assert lay0.padded % (world * 256) == 0 and lay0.padded >= lay0.total
         assert all(o % 64 == 0 for o in lay0.offsets)  # 128-byte aligned bf16 offsets
         covered = torch.zeros(lay0.padded, dtype=torch.int32)
         elems = 0

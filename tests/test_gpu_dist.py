@@ -100,3 +100,81 @@ def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle, fused, world):
                                        [1] * k, [1e-8] * k, wds, 1e-2, float(world), it + 1, 1)
     for a, b in zip(res[0]["params"], pc):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Drop-in use with a real module, modelled on the reference's apex/contrib/test/optimizers/test_dist_adam.py:84-156:
+# DistributedFusedAdam on each rank's own batch vs torch.optim.AdamW on the averaged gradients, tiny buckets so that
+# parameter fragments straddle shard boundaries, weight decay per param group, gradient clipping.
+def _module_worker(rank, world, port, outdir, clip):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+
+        torch.manual_seed(0)
+        mk = lambda: torch.nn.Sequential(*[torch.nn.Linear(7, 7) for _ in range(11)]).to(dev)   # test_dist_adam.py:60-66
+        model, ref = mk(), mk()
+        ref.load_state_dict(model.state_dict())
+        decay = [p for n, p in model.named_parameters() if n.endswith("weight")]
+        no_decay = [p for n, p in model.named_parameters() if n.endswith("bias")]
+        opt = DistributedFusedAdam([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
+                                   lr=1e-2, betas=(0.9, 0.95), eps=1e-8, bucket_cap_mb=71 * 4 / 2 ** 20)
+        assert opt.layout.nbuckets > 1 and opt.grads_flat.dtype == torch.float32
+        rdecay = [p for n, p in ref.named_parameters() if n.endswith("weight")]
+        rno = [p for n, p in ref.named_parameters() if n.endswith("bias")]
+        ropt = torch.optim.AdamW([{"params": rdecay, "weight_decay": 0.1}, {"params": rno, "weight_decay": 0.0}],
+                                 lr=1e-2, betas=(0.9, 0.95), eps=1e-8)
+        norms = []
+        for it in range(4):
+            opt.zero_grad()
+            ropt.zero_grad()
+            g = torch.Generator(device=dev).manual_seed(1000 * it + rank)
+            x = torch.randn(16, 7, device=dev, generator=g) * (3.0 if clip else 1.0)
+            model(x).pow(2).mean().backward()          # accumulates straight into the flat gradient buffer's views
+            ref(x).pow(2).mean().backward()
+            for p in ref.parameters():                 # DDP: average over ranks
+                dist.all_reduce(p.grad)
+                p.grad /= world
+            if clip:
+                rn = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
+                n = opt.step(max_grad_norm=0.5)
+                norms.append((float(n), float(rn)))
+            else:
+                opt.step()
+            ropt.step()
+        torch.cuda.synchronize()
+        out = {"mine": [p.detach().cpu() for p in model.parameters()], "ref": [p.detach().cpu() for p in ref.parameters()],
+               "norms": norms}
+        torch.save(out, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("clip", [False, True], ids=["plain", "clip_grad_norm"])
+def test_dist_adam_module_vs_ddp_adamw(tmp_path, clip):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+
+    world = 2
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_module_worker, args=(r, world, port, str(tmp_path), clip)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(500)
+        assert p.exitcode == 0
+    res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
+    for a, b in zip(res[0]["mine"], res[1]["mine"]):
+        assert torch.equal(a, b)                       # every rank holds the same gathered parameters
+    for a, b in zip(res[0]["mine"], res[0]["ref"]):
+        assert torch.allclose(a, b, rtol=2e-5, atol=2e-6)
+    for n, rn in res[0]["norms"]:
+        assert abs(n - rn) <= 1e-5 * rn
