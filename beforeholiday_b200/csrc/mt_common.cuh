@@ -78,35 +78,49 @@ template <> struct Elem<__nv_bfloat16> {
 // allocated in L1 (L1::no_allocate).  The non-coherent (.nc) path is deliberately NOT used even for input-only
 // lists: in-place calls, where an output list aliases an input list, are legal for this API
 // (/root/reference/tests/L0/run_amp/test_multi_tensor_scale.py:58-77).
+// Cache-policy qualifiers of the streaming accesses.  Swept on B200 (profiles/r1_cache_hint_sweep.log); overridable at
+// compile time for tools/tune_adam.cu.
+#ifndef MT_LD_HINT
+#define MT_LD_HINT ".L1::no_allocate"
+#endif
+#ifndef MT_ST_HINT
+#define MT_ST_HINT ".L1::no_allocate"
+#endif
+#ifndef MT_LD_HINT256   // 256-bit accesses additionally accept .L2::evict_* (ptxas rejects it on narrower ones)
+#define MT_LD_HINT256 MT_LD_HINT
+#endif
+#ifndef MT_ST_HINT256
+#define MT_ST_HINT256 MT_ST_HINT
+#endif
 template <int N, bool RO> struct RawVec;
 
 template <bool RO> struct RawVec<2, RO> {
     __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[2]) {
-        asm volatile("ld.global.L1::no_allocate.v2.b32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p) : "memory");
+        asm volatile("ld.global" MT_LD_HINT ".v2.b32 {%0,%1}, [%2];" : "=r"(w[0]), "=r"(w[1]) : "l"(p) : "memory");
     }
     __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[2]) {
-        asm volatile("st.global.L1::no_allocate.v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(w[0]), "r"(w[1]) : "memory");
+        asm volatile("st.global" MT_ST_HINT ".v2.b32 [%0], {%1,%2};" ::"l"(p), "r"(w[0]), "r"(w[1]) : "memory");
     }
 };
 template <bool RO> struct RawVec<4, RO> {
     __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[4]) {
-        asm volatile("ld.global.L1::no_allocate.v4.b32 {%0,%1,%2,%3}, [%4];"
+        asm volatile("ld.global" MT_LD_HINT ".v4.b32 {%0,%1,%2,%3}, [%4];"
                          : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "l"(p) : "memory");
     }
     __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[4]) {
-        asm volatile("st.global.L1::no_allocate.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w[0]), "r"(w[1]),
+        asm volatile("st.global" MT_ST_HINT ".v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(w[0]), "r"(w[1]),
                      "r"(w[2]), "r"(w[3]) : "memory");
     }
 };
 // 256-bit global accesses are an sm_100 addition (SASS: LDG.E.256 / STG.E.256).
 template <bool RO> struct RawVec<8, RO> {
     __device__ static __forceinline__ void ld(const void* p, uint32_t (&w)[8]) {
-        asm volatile("ld.global.L1::no_allocate.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        asm volatile("ld.global" MT_LD_HINT256 ".v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
                          : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
                          : "l"(p) : "memory");
     }
     __device__ static __forceinline__ void st(void* p, const uint32_t (&w)[8]) {
-        asm volatile("st.global.L1::no_allocate.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]),
+        asm volatile("st.global" MT_ST_HINT256 ".v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]),
                      "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
     }
 };

@@ -267,6 +267,11 @@ int main(int argc, char** argv) {
         ref_sum = checksum(B);
         cudaFree(t.blob);
     }
+    if (argc > 2) {  // quick mode (cache-hint sweep): only the product's launch shape, three times
+        for (int rep = 0; rep < 3; rep++)
+            run_lib<8, 1, 256, 4>("T256B4 ld" MT_LD_HINT "|" MT_LD_HINT256 " st" MT_ST_HINT "|" MT_ST_HINT256, B, hp, noop, 16384, false, sms, ref_sum);
+        return 0;
+    }
     run_lib<8, 1, 512, 2>("lib G8 U1 T512 B2 persistent", B, hp, noop, 16384, true, sms, ref_sum);
     for (int tile : {4096, 6144, 8192, 12288, 16384, 32768})
         run_lib<8, 1, 256, 4>("lib G8 U1 T256 B4 grid=ntiles", B, hp, noop, tile, false, sms, ref_sum);
