@@ -178,3 +178,53 @@ def test_dist_adam_module_vs_ddp_adamw(tmp_path, clip):
         assert torch.allclose(a, b, rtol=2e-5, atol=2e-6)
     for n, rn in res[0]["norms"]:
         assert abs(n - rn) <= 1e-5 * rn
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def _bucket_worker(rank, world, port, outdir):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from beforeholiday_b200.parallel import FlatBucketAllreduce
+
+        out = {}
+        for dt, fp32 in ((torch.float32, False), (torch.float16, True), (torch.bfloat16, False)):
+            g = torch.Generator(device=dev).manual_seed(7 + rank)
+            bucket = [torch.randint(-8, 8, (n,), device=dev, generator=g).to(dt) / 4 for n in (70001, 3, 4096)]
+            ref = [t.float().clone() for t in bucket]
+            for t in ref:
+                dist.all_reduce(t)
+                t /= world
+            red = FlatBucketAllreduce(bucket, gradient_predivide_factor=2.0, allreduce_always_fp32=fp32)
+            red()
+            assert red.overflow_buf.item() == 0
+            out[str(dt)] = all(torch.equal(a.float(), b) for a, b in zip(bucket, ref))   # small dyadic values: exact
+            bucket[1][0] = float("inf")
+            red()
+            out[str(dt) + "_flag"] = int(red.overflow_buf.item())
+        torch.save(out, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_flat_bucket_allreduce_two_gpus(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_bucket_worker, args=(r, 2, port, str(tmp_path))) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(500)
+        assert p.exitcode == 0
+    for r in range(2):
+        res = torch.load(tmp_path / f"rank{r}.pt")
+        assert all(v is True or v == 1 for v in res.values()), res
