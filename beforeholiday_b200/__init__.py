@@ -36,7 +36,7 @@ def load_amp_C():
 def install(as_apex: bool = True):
     """Register the extension under the reference's module names so unmodified callers find it.
 
-    After ``install()``: ``import amp_C`` and ``import distributed_adam_cuda`` resolve to this package's
+    After ``install()``: ``import amp_C``, ``import distributed_adam_cuda`` and ``import distributed_lamb_cuda`` resolve to this package's
     extension (the reference's optimizers do exactly those imports, e.g. apex/optimizers/fused_adam.py:75,
     apex/contrib/optimizers/distributed_fused_adam.py:291-293).
     """
@@ -44,4 +44,6 @@ def install(as_apex: bool = True):
     sys.modules.setdefault("amp_C", mod)
     if as_apex:
         sys.modules.setdefault("distributed_adam_cuda", mod)
+        sys.modules.setdefault("distributed_lamb_cuda", mod)   # apex/contrib/optimizers/distributed_fused_lamb.py:99-106
+        sys.modules.setdefault("fused_adam_cuda", mod)         # only maybe_cast_mt is carried over (:100, :856-861)
     return mod

@@ -21,7 +21,7 @@ OBJ = PKG / "build"
 NVCC = os.environ.get("MT_NVCC", "/usr/local/cuda/bin/nvcc")
 CXX = os.environ.get("MT_CXX", "/usr/bin/g++")
 
-LIB_SOURCES = ["mt_table.cu", "mt_api_scale.cu", "mt_api_norm.cu", "mt_api_optim.cu", "mt_api_noalloc.cu", "mt_api_p2p.cu", "mt_api_more.cu"]
+LIB_SOURCES = ["mt_table.cu", "mt_api_scale.cu", "mt_api_norm.cu", "mt_api_optim.cu", "mt_api_noalloc.cu", "mt_api_p2p.cu", "mt_api_more.cu", "mt_api_distlamb.cu"]
 LIB_HEADERS = ["mt_common.cuh", "mt_ops.cuh", "mt_host.h"]
 
 NVCC_FLAGS = [

@@ -421,6 +421,90 @@ void multi_tensor_fused_adam_capturable(int chunk_size, at::Tensor noop_flag, Te
                                                 step.data_ptr<int32_t>(), mode, f.stream));
 }
 
+// fused_adam_cuda.maybe_cast_mt (/root/reference/apex/contrib/csrc/optimizers/fused_adam_cuda.cpp:13,85)
+void maybe_cast_mt(int chunk_size, at::Tensor overflow_flag, TensorLists tensor_lists) {
+    Flat f;
+    TORCH_CHECK(py::len(tensor_lists) == 2, "expected tensor lists of size 2");
+    flatten(tensor_lists, 2, 2, "maybe_cast_mt", f);
+    check(mt_multi_tensor_maybe_cast(chunk_size, flag_ptr(overflow_flag), &f.tl, f.stream));
+}
+
+// distributed_lamb_cuda.multi_tensor_lamb_compute_update_term
+// (/root/reference/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp:3-17).  Two trailing optional
+// arguments switch on the fused per-parameter norm sums: `seg_begin` (CUDA int32[nseg+1]) and `model_dtype`
+// (torch dtype of the model parameters); the function then returns a CUDA float[2][nseg] tensor (else None).
+py::object multi_tensor_lamb_compute_update_term(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                                 at::Tensor per_tensor_beta1, at::Tensor per_tensor_beta2,
+                                                 at::Tensor per_tensor_beta3, at::Tensor per_tensor_bias_correction,
+                                                 at::Tensor step, at::Tensor per_tensor_epsilon, const int mode,
+                                                 at::Tensor per_tensor_decay, at::Tensor global_scale,
+                                                 at::Tensor global_grad_norm, const float max_grad_norm,
+                                                 c10::optional<at::Tensor> seg_begin,
+                                                 c10::optional<at::ScalarType> model_dtype) {
+    Flat f;
+    flatten(tensor_lists, 5, 5, "multi_tensor_lamb_compute_update_term", f);
+    const int64_t n = f.tl.ntensors;
+    TORCH_CHECK(per_tensor_beta1.numel() >= n && per_tensor_beta2.numel() >= n && per_tensor_bias_correction.numel() >= n &&
+                    per_tensor_epsilon.numel() >= n && per_tensor_decay.numel() >= n,
+                "per-tensor hyper-parameter tensors are shorter than the tensor lists");
+    TORCH_CHECK(per_tensor_beta1.scalar_type() == at::kFloat && per_tensor_beta2.scalar_type() == at::kFloat &&
+                    per_tensor_epsilon.scalar_type() == at::kFloat && per_tensor_decay.scalar_type() == at::kFloat &&
+                    global_scale.scalar_type() == at::kFloat && global_grad_norm.scalar_type() == at::kFloat,
+                "per-tensor hyper-parameters, global_scale and global_grad_norm must be float32 (the update term's type)");
+    TORCH_CHECK(per_tensor_bias_correction.scalar_type() == at::kInt && step.scalar_type() == at::kInt,
+                "per_tensor_bias_correction and step must be int32");
+    TORCH_CHECK(step.is_cuda() && global_scale.is_cuda() && global_grad_norm.is_cuda(),
+                "step, global_scale and global_grad_norm must be CUDA tensors");
+    const c10::cuda::CUDAGuard guard(f.device);
+    at::Tensor out, scratch;
+    const int32_t* seg = nullptr;
+    int nseg = 0, mdt = MT_F32;
+    size_t sbytes = 0;
+    if (seg_begin.has_value()) {
+        TORCH_CHECK(seg_begin->is_cuda() && seg_begin->scalar_type() == at::kInt && seg_begin->numel() >= 2,
+                    "seg_begin must be a CUDA int32 tensor of nseg+1 fragment indices");
+        nseg = (int)seg_begin->numel() - 1;
+        seg = seg_begin->data_ptr<int32_t>();
+        const at::ScalarType md = model_dtype.has_value() ? model_dtype.value() : at::kFloat;
+        mdt = md == at::kHalf ? MT_F16 : md == at::kBFloat16 ? MT_BF16 : MT_F32;
+        TORCH_CHECK(md == at::kHalf || md == at::kBFloat16 || md == at::kFloat, "model_dtype must be float32, float16 or bfloat16");
+        out = at::zeros({2, nseg}, f.first.options().dtype(at::kFloat).layout(at::kStrided));
+        sbytes = mt_dist_lamb_scratch_bytes(&f.tl);
+        scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)}, f.first.options().dtype(at::kByte).layout(at::kStrided));
+    }
+    check(mt_multi_tensor_lamb_compute_update_term(
+        chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(), per_tensor_beta2.data_ptr<float>(),
+        per_tensor_beta3.defined() && per_tensor_beta3.numel() ? per_tensor_beta3.data_ptr<float>() : nullptr,
+        per_tensor_bias_correction.data_ptr<int32_t>(), step.data_ptr<int32_t>(), per_tensor_epsilon.data_ptr<float>(),
+        mode, per_tensor_decay.data_ptr<float>(), global_scale.data_ptr<float>(), global_grad_norm.data_ptr<float>(),
+        max_grad_norm, seg, nseg, mdt, seg ? out.data_ptr<float>() : nullptr, seg ? scratch.data_ptr() : nullptr, sbytes,
+        f.stream));
+    if (seg) return py::cast(out);
+    return py::none();
+}
+
+// distributed_lamb_cuda.multi_tensor_lamb_update_weights (multi_tensor_distopt_lamb.cpp:19-29)
+void multi_tensor_lamb_update_weights(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
+                                      at::Tensor per_tensor_param_norm, at::Tensor per_tensor_update_norm,
+                                      at::Tensor update_norm_offset, at::Tensor learning_rate,
+                                      at::Tensor per_tensor_decay, at::Tensor global_grad_norm, bool use_nvlamb) {
+    Flat f;
+    flatten(tensor_lists, 3, 3, "multi_tensor_lamb_update_weights", f);
+    const int64_t n = f.tl.ntensors;
+    TORCH_CHECK(per_tensor_param_norm.numel() >= n && update_norm_offset.numel() >= n && per_tensor_decay.numel() >= n,
+                "per-tensor tensors are shorter than the tensor lists");
+    TORCH_CHECK(per_tensor_param_norm.scalar_type() == at::kFloat && per_tensor_update_norm.scalar_type() == at::kFloat &&
+                    learning_rate.scalar_type() == at::kFloat && per_tensor_decay.scalar_type() == at::kFloat,
+                "norms, learning_rate and per_tensor_decay must be float32 (the update term's type)");
+    TORCH_CHECK(update_norm_offset.scalar_type() == at::kLong, "update_norm_offset must be int64");
+    TORCH_CHECK(learning_rate.is_cuda() && update_norm_offset.is_cuda(), "learning_rate and update_norm_offset must be CUDA tensors");
+    check(mt_multi_tensor_lamb_update_weights(
+        chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_param_norm.data_ptr<float>(),
+        per_tensor_update_norm.data_ptr<float>(), update_norm_offset.data_ptr<int64_t>(), learning_rate.data_ptr<float>(),
+        per_tensor_decay.data_ptr<float>(), global_grad_norm.defined() && global_grad_norm.numel() ? global_grad_norm.data_ptr<float>() : nullptr,
+        use_nvlamb ? 1 : 0, f.stream));
+}
+
 // Fused reduce-scatter + Adam + all-gather over peer memory.  grad_ptrs / param_ptrs: every rank's flat buffer base
 // address as mapped in this process (e.g. torch.distributed._symmetric_memory handle.buffer_ptrs).
 void multi_tensor_fused_adam_p2p(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
@@ -494,6 +578,15 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
           py::arg("rank"), py::arg("grad_ptrs"), py::arg("param_ptrs"), py::arg("grad_multicast_ptr") = 0,
           py::arg("param_multicast_ptr") = 0);
+    m.def("maybe_cast_mt", &maybe_cast_mt, "Converting multi-tensor copy, skipped when the overflow flag is set");
+    m.def("multi_tensor_lamb_compute_update_term", &multi_tensor_lamb_compute_update_term,
+          "Sharded LAMB stage 1: update term (optionally with fused per-parameter norm sums)", py::arg("chunk_size"),
+          py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor_beta1"), py::arg("per_tensor_beta2"),
+          py::arg("per_tensor_beta3"), py::arg("per_tensor_bias_correction"), py::arg("step"),
+          py::arg("per_tensor_epsilon"), py::arg("mode"), py::arg("per_tensor_decay"), py::arg("global_scale"),
+          py::arg("global_grad_norm"), py::arg("max_grad_norm"), py::arg("seg_begin") = py::none(),
+          py::arg("model_dtype") = py::none());
+    m.def("multi_tensor_lamb_update_weights", &multi_tensor_lamb_update_weights, "Sharded LAMB stage 2: weight update");
     m.def("launch_count", []() { return mt_launch_count(); }, "kernels launched by libmt_b200.so since load");
     m.def("table_cache_stats", &table_cache_stats, "device tensor-table cache counters");
     m.def("table_cache_clear", [](int device) { check(mt_table_cache_clear(device)); });

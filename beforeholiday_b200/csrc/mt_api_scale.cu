@@ -24,6 +24,27 @@ extern "C" int mt_multi_tensor_scale(int chunk_size, int32_t* noop_flag, const M
     return MT_OK;
 }
 
+extern "C" int mt_multi_tensor_maybe_cast(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, void* stream_) {
+    using namespace mt;
+    (void)chunk_size;
+    int rc = validate_lists(tl, 2, 2, "maybe_cast_mt");
+    if (rc) return rc;
+    if (!noop_flag) return set_error(MT_EINVAL, "maybe_cast_mt: overflow_flag is NULL");
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    DeviceGuard guard(tl->device);
+    if (!guard.ok) return set_error(MT_ECUDA, "maybe_cast_mt: cannot select CUDA device %d", tl->device);
+    DevTable tb;
+    rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
+    if (rc) return rc;
+    MT_DISPATCH_FHB(tl->dtype[0], Tin, "maybe_cast_mt",
+        MT_DISPATCH_FHB(tl->dtype[1], Tout, "maybe_cast_mt", {
+            using Op = CastOp<Tin, Tout>;
+            typename Op::Params prm{0};
+            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+        }))
+    return MT_OK;
+}
+
 extern "C" int mt_multi_tensor_axpby(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, float a, float b,
                                      int arg_to_check, void* stream_) {
     using namespace mt;

@@ -32,6 +32,19 @@ template <class Tin, class Tout> struct ScaleOp : OpBase {
     __device__ __forceinline__ void finish(State& s, int32_t* noop) const { finish_finite(s, noop); }
 };
 
+// MaybeCastFunctor: apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:734-783 (fused_adam_cuda.maybe_cast_mt, the
+// flat-buffer -> model-parameter copy of the sharded optimizers).  A converting copy that does nothing when the flag
+// is set and never writes it.   lists: in, out
+template <class Tin, class Tout> struct CastOp : OpBase {
+    static constexpr int kLists = 2;
+    template <int D> using T = typename Types<Tin, Tout>::template at<D>;
+    static constexpr unsigned kRead = 0b01, kWrite = 0b10;
+    static constexpr bool kEarlyExit = true;
+    struct Params { int unused; };
+    __device__ explicit CastOp(const Params&) {}
+    __device__ __forceinline__ void elem(float (&x)[2], State&) const { x[1] = x[0]; }
+};
+
 // AxpbyFunctor: csrc/multi_tensor_axpby_kernel.cu:73-79.   lists: x, y, out
 template <class Tx, class Ty, class To> struct AxpbyOp : OpBase {
     static constexpr int kLists = 3;
@@ -674,6 +687,117 @@ template <class Tp, class Tu> struct LambStage2LegacyOp : OpBase {
     }
     __device__ __forceinline__ void elem(float (&x)[2], State&) const {
         x[0] = fsub(x[0], fmul(ratio, Elem<Tp>::round(x[1])));
+    }
+};
+
+// ------------------------------------------------------------------------------------------------
+// Sharded LAMB (the kernels behind apex.contrib.optimizers.DistributedFusedLAMB):
+// apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:119-321 (stage 1), :325-433 (stage 2).
+// Stage 1.  lists: g (Tg), p, m, v (fp32 shard state), u (fp32 update term).  Per-FRAGMENT hyper-parameters live in
+// device arrays; step, global_scale and the global gradient norm are device scalars; beta3 is 1 - beta1 whatever
+// per_tensor_beta3 holds (:140); the bias corrections are evaluated in the kernel (:142-148; double pow here and in
+// the oracle, as for lamb_mp).  The clip factor is folded into the un-scaling divisor (:133-137).
+// Extension (need_norms): the per-tile sums of round_Tn(p)^2 and u^2 are written to scratch, so neither of the two
+// norm passes the reference's Python runs around this kernel (distributed_fused_lamb.py:673-692) needs its own sweep:
+// the model parameter IS round_Tn(master) at every step boundary, so its norm can be taken from the master shard.
+template <class Tg, class Tn, int kMode> struct DistLambStage1Op : OpBase {
+    static constexpr int kLists = 5;
+    template <int D> using T = typename Types<Tg, float, float, float, float>::template at<D>;
+    static constexpr unsigned kRead = 0b01111, kWrite = 0b11100;
+    static constexpr bool kEarlyExit = true;
+    struct Params {
+        const float *beta1, *beta2, *eps, *decay;
+        const int32_t *bias_correction, *step;
+        const float *global_scale, *global_grad_norm;
+        float max_grad_norm;
+        float* partials;  // [2][ntiles]: round_Tn(p)^2 then u^2
+        uint32_t ntiles;
+        int need_norms;
+    };
+    using State = Sum2State;
+    Params p;
+    float cscale, b1, b2, b3, omb2, bc1, bc2, eps, decay;
+    int step, bc_on;
+    __device__ explicit DistLambStage1Op(const Params& q) : p(q), b1(-1.f), b2(-1.f), bc1(1.f), bc2(1.f), bc_on(-1) {
+        const float gs = __ldg(q.global_scale);
+        cscale = gs;
+        if (q.max_grad_norm > 0.f) {  // :134-137 -- the 1e-6 literal makes the quotient a double expression
+            const float c = (float)((double)q.max_grad_norm / ((double)fdiv(__ldg(q.global_grad_norm), gs) + 1e-6));
+            cscale = fdiv(gs, fminf(1.0f, c));
+        }
+        step = __ldg(q.step);
+    }
+    __device__ __forceinline__ void begin_tensor(int t) {
+        const float nb1 = __ldg(p.beta1 + t), nb2 = __ldg(p.beta2 + t);
+        const int on = __ldg(p.bias_correction + t) == 1;
+        eps = __ldg(p.eps + t); decay = __ldg(p.decay + t);
+        if (nb1 != b1 || nb2 != b2 || on != bc_on) {
+            b1 = nb1; b2 = nb2; bc_on = on;
+            b3 = fsub(1.f, b1); omb2 = fsub(1.f, b2);
+            bc1 = 1.f; bc2 = 1.f;
+            if (on) {
+                bc1 = (float)(1.0 - pow((double)b1, (double)step));
+                bc2 = (float)(1.0 - pow((double)b2, (double)step));
+            }
+        }
+    }
+    __device__ __forceinline__ void init(State& s) const { s.sp = 0.f; s.su = 0.f; }
+    __device__ __forceinline__ bool load(int d) const { return d != 1 || decay != 0.f || p.need_norms; }
+    __device__ __forceinline__ void elem(float (&x)[5], State& s) const {
+        const float wn = Elem<Tn>::round(x[1]);
+        s.sp = fadd(s.sp, fmul(wn, wn));
+        const float w = decay == 0.f ? 0.f : x[1];  // :203-208
+        float m = x[2], v = x[3];
+        float sg = fdiv(x[0], cscale);
+        if constexpr (kMode == 0) sg = fadd(sg, fmul(decay, w));
+        m = fadd(fmul(m, b1), fmul(b3, sg));
+        v = fadd(fmul(v, b2), fmul(fmul(omb2, sg), sg));
+        const float denom = fadd(fsqrt(fdiv(v, bc2)), eps);
+        float u = fdiv(fdiv(m, bc1), denom);
+        if constexpr (kMode != 0) u = fadd(u, fmul(decay, w));
+        s.su = fadd(s.su, fmul(u, u));
+        x[4] = u; x[2] = m; x[3] = v;
+    }
+    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+        if (p.need_norms) {
+            const float tp = block_sum<THREADS>(s.sp, smem);
+            const float tu = block_sum<THREADS>(s.su, smem);
+            if (threadIdx.x == 0) {
+                p.partials[tile] = tp; p.partials[p.ntiles + tile] = tu;
+                // the reference's two multi_tensor_l2norm calls raise the flag on a non-finite chunk sum, which
+                // makes stage 2 a no-op on this rank
+                if (!finite_f(tp) || !finite_f(tu)) *noop = 1;
+            }
+        }
+        s.sp = 0.f; s.su = 0.f;
+    }
+};
+
+// Stage 2.  lists: u (fp32), p (fp32), p_copy (Tc).  update_norm is indexed through update_norm_offset (:349-350).
+template <class Tc> struct DistLambStage2Op : OpBase {
+    static constexpr int kLists = 3;
+    template <int D> using T = typename Types<float, float, Tc>::template at<D>;
+    static constexpr unsigned kRead = 0b011, kWrite = 0b110;
+    static constexpr bool kEarlyExit = true;
+    struct Params {
+        const float *param_norm, *update_norm;
+        const int64_t* update_norm_offset;
+        const float *lr, *decay;
+        int use_nvlamb;
+    };
+    Params p;
+    float lr, ratio;
+    __device__ explicit DistLambStage2Op(const Params& q) : p(q), lr(__ldg(q.lr)), ratio(0.f) {}
+    __device__ __forceinline__ void begin_tensor(int t) {
+        ratio = lr;
+        if (p.use_nvlamb || __ldg(p.decay + t) != 0.0f) {
+            const float pn = p.param_norm[t], un = p.update_norm[p.update_norm_offset[t]];
+            ratio = (un != 0.0f && pn != 0.0f) ? fmul(lr, fdiv(pn, un)) : lr;
+        }
+    }
+    __device__ __forceinline__ void elem(float (&x)[3], State&) const {
+        const float w = fsub(x[1], fmul(ratio, x[0]));
+        x[1] = w; x[2] = w;
     }
 };
 

@@ -150,6 +150,44 @@ int mt_multi_tensor_lars(int chunk_size, int32_t* noop_flag, const MtTensorLists
                          float momentum, float dampening, int nesterov, int first_run, int wd_after_momentum, float scale,
                          int is_skipped, void* stream);
 
+/* Converting copy out = (Tout)in that does nothing when *noop_flag != 0 and never writes the flag.  Lists: [in, out],
+ * each f32/f16/bf16 (the reference's e5m2-in-a-byte packing belongs to its deprecated fused_adam_cuda optimizer and is
+ * not carried over).  Replaces fused_adam_cuda.maybe_cast_mt,
+ * /root/reference/apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:734-783,939-959. */
+int mt_multi_tensor_maybe_cast(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, void* stream);
+
+/* Sharded LAMB, stage 1 (update term).  Lists: [g, p, m, v, u]; g f32/f16/bf16, the rest f32 shard state.  All
+ * per_tensor_* arrays are DEVICE arrays of ntensors entries (one per parameter fragment); step, global_scale and
+ * global_grad_norm are DEVICE scalars; per_tensor_beta3 is accepted and ignored (the reference recomputes 1 - beta1).
+ * Does nothing when *noop_flag != 0.
+ * Extension (seg_sq_out != NULL): seg_begin is a DEVICE int32[nseg+1] of fragment indices splitting the fragment list
+ * into runs that belong to one model parameter; seg_sq_out (DEVICE float[2][nseg]) receives, per run, the sum of
+ * round_to(model_dtype)(p)^2 and the sum of u^2 over this rank's shard -- the inputs of the two per-parameter norms
+ * the reference computes with separate multi_tensor_l2norm sweeps (distributed_fused_lamb.py:673-692).  scratch:
+ * mt_dist_lamb_scratch_bytes() bytes, only needed with the extension.
+ * Replaces multi_tensor_lamb_compute_update_term_cuda,
+ * /root/reference/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp:3-17, _kernel.cu:119-321,435-474. */
+size_t mt_dist_lamb_scratch_bytes(const MtTensorLists* tl);
+int mt_multi_tensor_lamb_compute_update_term(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                             const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                             const float* per_tensor_beta3, const int32_t* per_tensor_bias_correction,
+                                             const int32_t* step, const float* per_tensor_epsilon, int mode,
+                                             const float* per_tensor_decay, const float* global_scale,
+                                             const float* global_grad_norm, float max_grad_norm,
+                                             const int32_t* seg_begin, int nseg, int model_dtype, float* seg_sq_out,
+                                             void* scratch, size_t scratch_bytes, void* stream);
+
+/* Sharded LAMB, stage 2 (weight update).  Lists: [u (f32), p (f32), p_copy (f32/f16/bf16)].  per_tensor_param_norm is
+ * indexed by fragment, per_tensor_update_norm through update_norm_offset[fragment] (DEVICE int64[ntensors]);
+ * learning_rate is a DEVICE scalar; global_grad_norm is accepted and ignored, as in the reference.  Does nothing when
+ * *noop_flag != 0.  Replaces multi_tensor_lamb_update_weights_cuda,
+ * /root/reference/apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp:19-29, _kernel.cu:325-433,476-506. */
+int mt_multi_tensor_lamb_update_weights(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                        const float* per_tensor_param_norm, const float* per_tensor_update_norm,
+                                        const int64_t* update_norm_offset, const float* learning_rate,
+                                        const float* per_tensor_decay, const float* global_grad_norm, int use_nvlamb,
+                                        void* stream);
+
 /* Legacy split LAMB.  stage1 lists: [g, p, m, v, update]; per_tensor_decay is a DEVICE float[ntensors];
  * clipped_global_grad_norm is passed by value (the reference reads the norm on the host,
  * csrc/multi_tensor_lamb_stage_1.cu:126-127).  Arithmetic is carried out in the parameter dtype.

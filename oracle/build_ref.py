@@ -12,6 +12,8 @@ are copied into this repository):
                                                    (reference recipe: setup.py:313-336, flags :310-311)
   oracle/_ref/distributed_adam_cuda<EXT_SUFFIX> <- apex/contrib/csrc/optimizers/multi_tensor_distopt_adam{.cpp,_kernel.cu}
                                                    (reference recipe: setup.py, "--distributed_adam")
+  oracle/_ref/distributed_lamb_cuda<EXT_SUFFIX> <- apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb{.cpp,_kernel.cu}
+                                                   (reference recipe: setup.py, "--distributed_lamb")
 
 The reference's setup.py cannot run on a CUDA build of torch (setup.py:157 parses
 torch.version.hip unconditionally), so the same flags are issued directly with
@@ -68,6 +70,10 @@ def _compile(src: Path, name: str, inc, extra_inc):
             "-O3", "--use_fast_math", "-lineinfo", "-std=c++17",
             "--expt-relaxed-constexpr", "--expt-extended-lambda",
             "-Xcompiler", "-fPIC", "-w",
+            # what torch.utils.cpp_extension.CUDAExtension always adds (COMMON_NVCC_FLAGS); without them
+            # c10::Half comparisons in multi_tensor_distopt_lamb_kernel.cu:352 are ambiguous
+            "-D__CUDA_NO_HALF_OPERATORS__", "-D__CUDA_NO_HALF_CONVERSIONS__",
+            "-D__CUDA_NO_BFLOAT16_CONVERSIONS__", "-D__CUDA_NO_HALF2_OPERATORS__",
         ] + _common_defs(name) + incs
     else:
         cmd = [CXX, "-c", str(src), "-o", str(obj), "-O3", "-std=c++17", "-fPIC", "-w"] \
@@ -97,6 +103,10 @@ def build(jobs: int | None = None) -> list[Path]:
         "distributed_adam_cuda": [
             REF / "apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp",
             REF / "apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu",
+        ],
+        "distributed_lamb_cuda": [
+            REF / "apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp",
+            REF / "apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu",
         ],
     }
     jobs = jobs or os.cpu_count() or 4

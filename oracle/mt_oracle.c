@@ -516,6 +516,72 @@ void orc_lamb_mp_stage2(const void* u, int g_dt, void* p, int p_dt, void* out, i
     }
 }
 
+/* ---------------------------------------------------------------- sharded LAMB (apex/contrib/csrc/optimizers) */
+
+/* DistOptLAMBStage1Functor<T=float, GRAD_T, MATH_T=float>:
+ * apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:133-148 (scalars), :212-249 / :283-304 (element).
+ * combined_scale folds the clip factor into the loss-scale divisor; the "+ 1e-6" literal makes that quotient a double
+ * expression.  beta3 = 1 - beta1 regardless of the per-tensor beta3 array.  bias corrections: double pow rounded to
+ * float (the reference's fast-math device pow differs in the last ulps, as for lamb_mp).
+ * sq_out (may be NULL): [0] += sum round_to(model_dt)(p)^2, [1] += sum u^2 -- double accumulation; this is what the
+ * product's fused norm extension is checked against (to 1e-5 relative). */
+void orc_dist_lamb_stage1(const void* g, int g_dt, const float* p, float* m, float* v, float* u, int64_t n,
+                          float beta1, float beta2, int bias_correction, int step, float eps, int mode, float decay,
+                          float global_scale, float global_grad_norm, float max_grad_norm, int model_dt,
+                          double* sq_out) {
+    float cs = global_scale;
+    if (max_grad_norm > 0) {
+        float q = global_grad_norm / global_scale;
+        cs = (float)((double)max_grad_norm / ((double)q + 1e-6));
+        cs = global_scale / (1.0f < cs ? 1.0f : cs);
+    }
+    const float beta3 = 1 - beta1;
+    float bc1 = 1.0f, bc2 = 1.0f;
+    if (bias_correction == 1) {
+        bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+        bc2 = (float)(1.0 - pow((double)beta2, (double)step));
+    }
+    const float omb2 = 1 - beta2;
+    double sp = 0.0, su = 0.0;
+#pragma omp parallel for schedule(static) reduction(+ : sp, su)
+    for (int64_t i = 0; i < n; i++) {
+        float rg = ld(g, g_dt, i), rm = m[i], rv = v[i];
+        float rp = (decay == 0) ? 0.f : p[i];
+        float pm = rnd(p[i], model_dt);
+        sp += (double)pm * (double)pm;
+        float sg = rg / cs;
+        if (mode == 0) { float dp = decay * rp; sg = sg + dp; }
+        float t1 = rm * beta1, t2 = beta3 * sg;
+        rm = t1 + t2;
+        float t3 = rv * beta2, t4 = omb2 * sg; t4 = t4 * sg;
+        rv = t3 + t4;
+        float mu = rm / bc1, vu = rv / bc2;
+        float denom = sqrtf(vu) + eps;
+        float q = mu / denom;
+        float uu;
+        if (mode == 0) uu = q; else { float dp = decay * rp; uu = q + dp; }
+        su += (double)uu * (double)uu;
+        u[i] = uu; m[i] = rm; v[i] = rv;
+    }
+    if (sq_out) { sq_out[0] += sp; sq_out[1] += su; }
+}
+
+/* DistOptLAMBStage2Functor: multi_tensor_distopt_lamb_kernel.cu:342-351 (ratio), :376-383 / :407-419 (element).
+ * p_copy (copy_dt) = convert(new p). */
+void orc_dist_lamb_stage2(const float* u, float* p, void* p_copy, int copy_dt, int64_t n, float lr, float decay,
+                          int use_nvlamb, float param_norm, float update_norm) {
+    float ratio = lr;
+    if (use_nvlamb || decay != 0.0f)
+        ratio = (update_norm != 0.0f && param_norm != 0.0f) ? lr * (param_norm / update_norm) : lr;
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        float ru = ratio * u[i];
+        float w = p[i] - ru;
+        p[i] = w;
+        st(p_copy, copy_dt, i, w);
+    }
+}
+
 /* ---------------------------------------------------------------- Adagrad / NovoGrad / LARS */
 
 /* AdagradFunctor: csrc/multi_tensor_adagrad.cu:63-72. */

@@ -287,3 +287,50 @@ def convert(src: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     out = torch.empty(src.shape, dtype=dtype)
     lib().orc_convert(_p(src), DT[src.dtype], _p(out), DT[dtype], C.c_int64(src.numel()))
     return out
+
+
+# ---- sharded LAMB (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb.cpp:3-29) ----------------------------------
+def multi_tensor_lamb_compute_update_term(chunk_size, noop_flag, tensor_lists, per_tensor_beta1, per_tensor_beta2,
+                                          per_tensor_beta3, per_tensor_bias_correction, step, per_tensor_epsilon, mode,
+                                          per_tensor_decay, global_scale, global_grad_norm, max_grad_norm,
+                                          model_dtype=None):
+    """Lists [g, p, m, v, u] of CPU tensors (p, m, v, u float32).  Returns a float64 [2, ntensors] tensor of the
+    per-fragment sums of round_model(p)^2 and u^2 (the product's norm extension is checked against it)."""
+    _check_lists(tensor_lists, 5)
+    n = len(tensor_lists[0])
+    sq = torch.zeros(2, n, dtype=torch.float64)
+    if int(noop_flag.item()) != 0:
+        return sq
+    L = lib()
+    mdt = DT[model_dtype] if model_dtype is not None else 0
+    for i, (g, p, m, v, u) in enumerate(zip(*tensor_lists)):
+        assert p.dtype == m.dtype == v.dtype == u.dtype == torch.float32
+        out = (C.c_double * 2)(0.0, 0.0)
+        L.orc_dist_lamb_stage1(_p(g), DT[g.dtype], _p(p), _p(m), _p(v), _p(u), C.c_int64(g.numel()),
+                               _f(per_tensor_beta1[i]), _f(per_tensor_beta2[i]), C.c_int(int(per_tensor_bias_correction[i])),
+                               C.c_int(int(step)), _f(per_tensor_epsilon[i]), C.c_int(mode), _f(per_tensor_decay[i]),
+                               _f(float(global_scale)), _f(float(global_grad_norm)), _f(max_grad_norm), C.c_int(mdt), out)
+        sq[0, i], sq[1, i] = out[0], out[1]
+    return sq
+
+
+def multi_tensor_lamb_update_weights(chunk_size, noop_flag, tensor_lists, per_tensor_param_norm, per_tensor_update_norm,
+                                     update_norm_offset, learning_rate, per_tensor_decay, global_grad_norm, use_nvlamb):
+    """Lists [u, p, p_copy] of CPU tensors (u, p float32)."""
+    _check_lists(tensor_lists, 3)
+    if int(noop_flag.item()) != 0:
+        return
+    L = lib()
+    for i, (u, p, c) in enumerate(zip(*tensor_lists)):
+        L.orc_dist_lamb_stage2(_p(u), _p(p), _p(c), DT[c.dtype], C.c_int64(u.numel()), _f(float(learning_rate)),
+                               _f(per_tensor_decay[i]), C.c_int(bool(use_nvlamb)), _f(per_tensor_param_norm[i]),
+                               _f(per_tensor_update_norm[int(update_norm_offset[i])]))
+
+
+def maybe_cast_mt(chunk_size, overflow_flag, tensor_lists):
+    """apex/contrib/csrc/optimizers/fused_adam_cuda_kernel.cu:734-783: converting copy, skipped when the flag is set."""
+    _check_lists(tensor_lists, 2)
+    if int(overflow_flag.item()) != 0:
+        return
+    for a, b in zip(*tensor_lists):
+        b.copy_(a.to(b.dtype))

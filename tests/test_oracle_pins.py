@@ -231,3 +231,46 @@ def test_dist_adam_matches_adamw_and_copy(oracle):
                                        1024.0, it + 1, 1)
     assert rel_close(p, ref.data, 1e-6, 1e-8)
     assert bits_equal(pc, p.bfloat16())
+
+
+def test_dist_lamb_stages_reproduce_pinned_lamb(oracle):
+    """The sharded-LAMB restatement (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu) run as
+    stage 1 -> per-tensor norms -> stage 2 must reproduce, bit for bit, the multi_tensor_lamb restatement that is pinned
+    against the reference's RefLAMB above, when nothing clips and the loss scale is 1 (same functor arithmetic)."""
+    sizes = [5001, 33, 70001]
+    n = len(sizes)
+    for mode, wd, nv in ((1, 0.01, False), (0, 0.01, True), (1, 0.0, True)):
+        ps = [gen_inputs(100 + i, k).abs() * 0.5 + 0.01 for i, k in enumerate(sizes)]
+        ms, vs = [torch.zeros(k) for k in sizes], [torch.zeros(k) for k in sizes]
+        ps2, ms2, vs2 = [p.clone() for p in ps], [m.clone() for m in ms], [v.clone() for v in vs]
+        us = [torch.zeros(k) for k in sizes]
+        copies = [torch.zeros(k, dtype=torch.float16) for k in sizes]
+        for it in range(3):
+            gs = [gen_inputs(1000 + 10 * it + i, k) * 0.1 for i, k in enumerate(sizes)]
+            gs2 = [g.clone() for g in gs]
+            f = flag()
+            gnorm, _ = oracle.multi_tensor_l2norm(65536, f, [gs], False)
+            oracle.multi_tensor_lamb(8192, f, [gs, ps, ms, vs], 5e-4, 0.9, 0.999, 1e-6, it + 1, 1, wd, 1, mode, gnorm, 1e30, nv)
+            _, pn = oracle.multi_tensor_l2norm(8192, f, [ps2], True)    # multi_tensor_lamb norms with ITS chunk size
+            oracle.multi_tensor_lamb_compute_update_term(8192, f, [gs2, ps2, ms2, vs2, us], [0.9] * n, [0.999] * n, [0.0] * n,
+                                                         [1] * n, it + 1, [1e-6] * n, mode, [wd] * n, 1.0, gnorm, 0.0)
+            _, un = oracle.multi_tensor_l2norm(8192, f, [us], True)
+            oracle.multi_tensor_lamb_update_weights(8192, f, [us, ps2, copies], pn, un, list(range(n)), 5e-4, [wd] * n, gnorm, nv)
+        for a, b in zip(ps + ms + vs, ps2 + ms2 + vs2):
+            assert bits_equal(a, b)
+        for c, p in zip(copies, ps2):
+            assert bits_equal(c, p.half())
+
+
+def test_dist_lamb_combined_scale(oracle):
+    """combined_scale = global_scale / min(1, max_norm / (gnorm/global_scale + 1e-6)) (:133-137): unscaling and
+    clipping in one divisor."""
+    g = gen_inputs(7, 4099) * 64
+    p, m, v, u = gen_inputs(8, 4099), torch.zeros(4099), torch.zeros(4099), torch.zeros(4099)
+    gnorm = g.double().norm().float()
+    oracle.multi_tensor_lamb_compute_update_term(8192, flag(), [[g], [p], [m], [v], [u]], [0.9], [0.999], [0.0], [0], 1,
+                                                 [1e-6], 1, [0.0], 64.0, gnorm, 1.0)
+    cs = 64.0 / min(1.0, 1.0 / (float(gnorm) / 64.0 + 1e-6))
+    want_m = (1 - torch.tensor(0.9)) * (g / torch.tensor(cs, dtype=torch.float32))
+    assert rel_close(m, want_m, 1e-6, 1e-9)
+    assert abs(float((g / cs).double().norm()) - 1.0) < 1e-4      # the clipped, unscaled gradient has norm max_norm
