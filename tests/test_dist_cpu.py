@@ -143,3 +143,127 @@ def test_sharded_step_world2_matches_single_process(tmp_path):
                                   [1] * k, [1e-8] * k, wds, 1e-2, float(world), it + 1, 1)
     for a, b in zip(results[0], pc):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Sharded LAMB: host logic of DistributedFusedLAMB (fragment runs, per-parameter norm exchange, overflow/step handling)
+LAMB_SIZES = [1000, 7, 40000, 33333, 1, 129]      # 40000 and 33333 straddle several sub-shards
+
+
+def _lamb_cls():
+    from beforeholiday_b200.contrib.optimizers import DistributedFusedLAMB
+
+    class CpuShardedLamb(DistributedFusedLAMB):
+        """gloo + oracle stand-ins for the NCCL collectives and the CUDA kernels."""
+
+        def _init_comm(self):
+            self.rs_group = self.ag_group = self.group
+            self.ag_stream = None
+
+        def _reduce_scatter(self, b):
+            lo, hi = self.layout.bucket_range(b)
+            buf = self.grads_flat[lo:hi].float() / self.world
+            dist.all_reduce(buf, group=self.group)
+            olo, ohi = self.layout.owned_range(b)
+            self.grads_flat[olo:ohi].copy_(buf[olo - lo:ohi - lo])
+
+        def _all_gather(self, b):
+            lo, hi = self.layout.bucket_range(b)
+            olo, ohi = self.layout.owned_range(b)
+            parts = [torch.empty(self.layout.sub_shard, dtype=torch.float32) for _ in range(self.world)]
+            dist.all_gather(parts, self.params_flat[olo:ohi].float().contiguous(), group=self.group)
+            self.params_flat[lo:hi].copy_(torch.cat(parts))
+
+        def _shard_sq_norm(self):
+            L = self.layout
+            return sum((self.grads_flat[slice(*L.owned_range(b))].double() ** 2).sum() for b in range(L.nbuckets)).float().reshape(1)
+
+        def _stage1(self, gs, gnorm, max_grad_norm):
+            from oracle import mt_oracle as O
+
+            if not self.frags:
+                return None
+            sq = O.multi_tensor_lamb_compute_update_term(
+                8192, self._overflow_buf, self._stage1_lists, self._beta1.tolist(), self._beta2.tolist(), None,
+                self._bias_correction.tolist(), int(self._step), self._eps.tolist(), self._adam_w_mode,
+                self._decay.tolist(), float(gs), float(gnorm), max_grad_norm, self.model_dtype)
+            seg = self._seg_begin.tolist()
+            return torch.stack([torch.stack([sq[s, seg[k]:seg[k + 1]].sum() for k in range(len(seg) - 1)])
+                                for s in range(2)]).float()
+
+        def _stage2(self, b, param_norm, update_norm, gnorm):
+            from oracle import mt_oracle as O
+
+            i, j = self._bucket_frag_range[b]
+            if i < j:
+                O.multi_tensor_lamb_update_weights(8192, self._overflow_buf, [l[i:j] for l in self._stage2_lists],
+                                                   param_norm[i:j].tolist(), update_norm.tolist(), self._offsets[i:j].tolist(),
+                                                   float(self._lr), self._decay[i:j].tolist(), float(gnorm), self._use_nvlamb)
+
+    return CpuShardedLamb
+
+
+def _lamb_worker(rank, world, port, outdir):
+    import sys
+
+    sys.path.insert(0, os.path.dirname(__file__))
+    from lamb_replay import make_grad
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        params = [torch.nn.Parameter((torch.randn(n) * 0.05).bfloat16()) for n in LAMB_SIZES]
+        groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
+        opt = _lamb_cls()(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, use_nvlamb=False,
+                          dwu_num_blocks=2, dwu_num_chunks=2, device="cpu")
+        assert opt.layout.nbuckets > 1
+        assert any(sum(1 for f in opt.frags if f.param == q) > 1 for q in range(len(LAMB_SIZES)))  # multi-fragment runs
+        opt.set_global_scale(64.0)
+        order = params[0::2] + params[1::2]      # the optimizer's flat order
+        for it in range(4):
+            for i, p in enumerate(order):
+                p.grad.copy_(make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape))
+            if it == 2 and rank == 1:
+                order[3].grad.view(-1)[5] = float("inf")       # one rank overflows: every rank must skip the step
+            opt.complete_reductions()
+            opt.step()
+            assert int(opt._overflow_buf) == (1 if it == 2 else 0)
+        assert int(opt._step) == 3
+        torch.save([p.detach().clone() for p in order], os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_sharded_lamb_world2_matches_single_process(tmp_path):
+    import sys
+
+    sys.path.insert(0, os.path.dirname(__file__))
+    from lamb_replay import replay
+    from oracle import mt_oracle as O
+
+    world = 2
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    res = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
+    for a, b in zip(res[0], res[1]):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    torch.manual_seed(0)
+    init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
+    order = init[0::2] + init[1::2]
+    sizes = [x.numel() for x in order]
+    props = [(0.01, 1, 0.9, 0.999, 1e-6)] * len(init[0::2]) + [(0.0, 1, 0.9, 0.999, 1e-6)] * len(init[1::2])
+    _, pc, step = replay(O, sizes, order, props, world, 4, torch.bfloat16, 2e-3, 64.0, 1.0, 1, False,
+                         lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2)
+    assert step == 3
+    for a, b in zip(res[0], pc):
+        ia, ib = a.view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
+        assert int((ia - ib).abs().max()) <= 1          # bf16 copies within 1 ulp (norm summation order)
+        assert float((ia != ib).float().mean()) < 0.01

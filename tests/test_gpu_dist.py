@@ -228,3 +228,88 @@ def test_flat_bucket_allreduce_two_gpus(tmp_path):
     for r in range(2):
         res = torch.load(tmp_path / f"rank{r}.pt")
         assert all(v is True or v == 1 for v in res.values()), res
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+LAMB_SIZES = [1000, 7, 40000, 333333, 1, 129]
+
+
+def _lamb_worker(rank, world, port, outdir):
+    import sys
+
+    import torch.distributed as dist
+
+    sys.path.insert(0, os.path.dirname(__file__))
+    from lamb_replay import make_grad
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from beforeholiday_b200.contrib.optimizers import DistributedFusedLAMB
+
+        torch.manual_seed(0)
+        init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
+        params = [torch.nn.Parameter(x.clone().to(dev)) for x in init]
+        groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
+        opt = DistributedFusedLAMB(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, dwu_num_blocks=2,
+                                   dwu_num_chunks=2)
+        opt.set_global_scale(64.0)
+        order = params[0::2] + params[1::2]
+        launches = []
+        for it in range(4):
+            for i, p in enumerate(order):
+                p.grad.copy_(make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape))
+            if it == 2 and rank == world - 1:
+                order[3].grad.view(-1)[5] = float("inf")
+            l0 = opt._amp_C().launch_count()
+            opt.complete_reductions()
+            opt.step()
+            launches.append(opt._amp_C().launch_count() - l0)
+            assert int(opt._overflow_buf) == (1 if it == 2 else 0)
+        torch.cuda.synchronize()
+        torch.save({"params": [p.detach().cpu() for p in order], "step": int(opt._step), "launches": launches,
+                    "nbuckets": opt.layout.nbuckets}, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("world", [2, 4])
+def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import sys
+
+    import torch.multiprocessing as mp
+
+    sys.path.insert(0, os.path.dirname(__file__))
+    from lamb_replay import replay
+    from oracle import mt_oracle as O
+
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(500)
+        assert p.exitcode == 0
+    res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
+    for r in range(1, world):
+        for a, b in zip(res[0]["params"], res[r]["params"]):
+            assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    assert all(x["step"] == 3 for x in res)
+    # l2norm (2 launches) + stage 1 (+ its run finalize) + one stage-2 launch per bucket that holds fragments
+    assert all(n <= 4 + res[0]["nbuckets"] for n in res[0]["launches"]), res[0]["launches"]
+    torch.manual_seed(0)
+    init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
+    order = init[0::2] + init[1::2]
+    props = [(0.01, 1, 0.9, 0.999, 1e-6)] * 3 + [(0.0, 1, 0.9, 0.999, 1e-6)] * 3
+    _, pc, _ = replay(O, [x.numel() for x in order], order, props, world, 4, torch.bfloat16, 2e-3, 64.0, 1.0, 1, False,
+                      lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2)
+    for a, b in zip(res[0]["params"], pc):
+        ia, ib = a.reshape(-1).view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
+        assert int((ia - ib).abs().max()) <= 1
+        assert float((ia != ib).float().mean()) < 0.01

@@ -195,3 +195,62 @@ def test_vs_reference_cuda(amp_C):
             ref.multi_tensor_lamb_update_weights(8192, flag(), [l2[4], p2, copies2], pn, un, off, t([2e-3]), wd, gnorm, nv)
             for a, b in zip(p1 + copies1, p2 + copies2):
                 check_close(a, b, f"update_weights nvlamb={nv}")
+
+
+# ------------------------------------------------------------------------------------------------ the optimizer class
+LAMB_SIZES = [1000, 7, 40000, 333333, 1, 129]
+
+
+def _check_vs_replay(got, want_pc, dtype):
+    for a, b in zip(got, want_pc):
+        a = a.detach().cpu().reshape(-1)
+        if dtype == F32:
+            assert torch.allclose(a, b, rtol=2e-6, atol=1e-8)
+        else:
+            ia, ib = a.view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
+            assert int((ia - ib).abs().max()) <= 1
+            assert float((ia != ib).float().mean()) < 0.01
+
+
+@pytest.mark.parametrize("dtype", [BF16, F16, F32])
+@pytest.mark.parametrize("mode,use_nvlamb,max_norm", [(1, False, 1.0), (0, True, 0.0)])
+def test_distributed_fused_lamb_single_gpu_matches_oracle_replay(oracle, dtype, mode, use_nvlamb, max_norm):
+    """world = 1 (no process group): the whole pipeline -- norm, overflow/step bookkeeping on the device, stage 1 with the
+    fused per-parameter norm sums, stage 2 per bucket -- against the oracle applied to whole parameters."""
+    from beforeholiday_b200.contrib.optimizers import DistributedFusedLAMB
+    from lamb_replay import make_grad, replay
+
+    torch.manual_seed(0)
+    init = [(torch.randn(n) * 0.05).to(dtype) for n in LAMB_SIZES]
+    params = [torch.nn.Parameter(x.clone().cuda()) for x in init]
+    groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
+    opt = DistributedFusedLAMB(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=max_norm,
+                               adam_w_mode=bool(mode), use_nvlamb=use_nvlamb, dwu_num_blocks=2, dwu_num_chunks=2)
+    assert opt.layout.nbuckets == 4
+    opt.set_global_scale(torch.tensor([64.0], device="cuda"))
+    order = params[0::2] + params[1::2]
+    for it in range(4):
+        for i, p in enumerate(order):
+            p.grad.copy_(make_grad(1000 * it + i, p.numel(), dtype, 64.0).view(p.shape))
+        if it == 2:
+            order[3].grad.view(-1)[5] = float("nan")
+        opt.complete_reductions()
+        opt.step()
+        assert int(opt._overflow_buf) == (1 if it == 2 else 0)
+    assert int(opt._step) == 3 and int(opt.state_dict()['step']) == 3
+    oi = init[0::2] + init[1::2]
+    props = [(0.01, 1, 0.9, 0.999, 1e-6)] * 3 + [(0.0, 1, 0.9, 0.999, 1e-6)] * 3
+    p32, pc, _ = replay(oracle, [x.numel() for x in oi], oi, props, 1, 4, dtype, 2e-3, 64.0, max_norm, mode, use_nvlamb,
+                        lambda it, r, i: 1000 * it + i, overflow_at=2)
+    _check_vs_replay(order, pc, dtype)
+    # the fp32 masters of the shard (= everything at world 1) follow the replay to norm-rounding accuracy
+    for f in opt.frags:
+        n = f.flat_hi - f.flat_lo
+        a = opt._fp32_p[f.state_lo:f.state_lo + n].cpu()
+        b = p32[f.param][f.param_lo:f.param_lo + n]
+        assert torch.allclose(a, b, rtol=2e-6, atol=1e-8)
+    # checkpoint round trip
+    sd = {k: v.clone() for k, v in opt.state_dict().items()}
+    opt._fp32_p.zero_()
+    opt.load_state_dict(sd)
+    assert torch.equal(opt._fp32_p, sd['fp32_p'])
