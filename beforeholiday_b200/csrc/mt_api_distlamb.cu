@@ -12,8 +12,10 @@
 namespace mt {
 
 constexpr int kSegThreads = 256;
-// Stage 1 moves five lists and keeps two norm accumulators: at 4 CTAs/SM (64 registers) ptxas spills up to 188 bytes
-// per thread inside the element loop; 3 CTAs/SM (80 registers) is spill-free.
+// Stage 1 moves five lists and keeps two norm accumulators live across the IEEE-division slow-path calls: at 4 CTAs/SM
+// (64 registers) ptxas spills up to 188 bytes per thread inside the element loop; 3 CTAs/SM (80 registers) is
+// spill-free.  Measured on a 336 M-element shard (tools/bench_ops.py --configs c6, profiles/r1_ops_sharded_lamb.jsonl):
+// 1.484 ms vs 1.502 ms -- no difference beyond noise, so the spill-free build is kept.
 constexpr int kStage1MinBlocks = 3;
 
 // partials: [2][ntiles] per-tile sums.  out: [2][nseg] sums (NOT square-rooted: they are all-reduced first).

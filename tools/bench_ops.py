@@ -191,6 +191,58 @@ def main():
                    launches_of(lamb_step) if mod is mine else None,
                    {"bytes_per_param": 44 if mod is mine else 52})
 
+    if "c6" in cfgs:
+        # sharded LAMB kernels on a BERT-large-sized shard: fp16 grads and model copy, fp32 p/m/v/u
+        shapes = workloads.bert_large()
+        P = workloads.total(shapes)
+        nt = len(shapes)
+        g16 = alloc(shapes, torch.float16, 1.0)
+        p, m, v, u = (alloc(shapes, torch.float32) for _ in range(4))
+        v = [t.abs() for t in v]
+        p16 = [t.half() for t in p]
+        T = lambda val, dt=torch.float32: torch.full((nt,), val, dtype=dt, device="cuda")
+        hp = (T(0.9), T(0.999), T(0.1), T(1, torch.int32))
+        eps, wd = T(1e-6), T(0.01)
+        step, gs, lr = (torch.tensor([v_], dtype=dt, device="cuda") for v_, dt in ((3, torch.int32), (128.0, torch.float32), (1e-4, torch.float32)))
+        gn = torch.tensor([4000.0], device="cuda")
+        off = torch.arange(nt, device="cuda")
+        seg = torch.arange(nt + 1, dtype=torch.int32, device="cuda")
+        dl = load_ref("distributed_lamb_cuda")
+
+        def mine_step():
+            sq = mine.multi_tensor_lamb_compute_update_term(8192, flag, [g16, p, m, v, u], *hp, step, eps, 1, wd, gs, gn, 1.0,
+                                                            seg, torch.float16)
+            n = sq.sqrt()
+            mine.multi_tensor_lamb_update_weights(8192, flag, [u, p, p16], n[0], n[1], off, lr, wd, gn, False)
+        ms, host = timeit(mine_step, args.iters)
+        report("C6 sharded LAMB, 336M-param shard", "stage1 (+fused norms) + stage2 (40 B/param)", "b200", ms, host, 40 * P, P,
+               launches_of(mine_step))
+        fn = lambda: mine.multi_tensor_lamb_compute_update_term(8192, flag, [g16, p, m, v, u], *hp, step, eps, 1, wd, gs, gn, 1.0, seg, torch.float16)
+        ms, host = timeit(fn, args.iters)
+        report("C6 sharded LAMB, 336M-param shard", "stage1 + fused norms (26 B/param)", "b200", ms, host, 26 * P, P)
+        fn = lambda: mine.multi_tensor_lamb_compute_update_term(8192, flag, [g16, p, m, v, u], *hp, step, eps, 1, wd, gs, gn, 1.0)
+        ms, host = timeit(fn, args.iters)
+        report("C6 sharded LAMB, 336M-param shard", "stage1 (26 B/param)", "b200", ms, host, 26 * P, P)
+        n2 = torch.ones(2, nt, device="cuda")
+        fn = lambda: mine.multi_tensor_lamb_update_weights(8192, flag, [u, p, p16], n2[0], n2[1], off, lr, wd, gn, False)
+        ms, host = timeit(fn, args.iters)
+        report("C6 sharded LAMB, 336M-param shard", "stage2 (14 B/param)", "b200", ms, host, 14 * P, P)
+        if dl is not None and ref is not None:
+            def ref_step():
+                _, pn = ref.multi_tensor_l2norm(65536, flag, [p16], True)
+                dl.multi_tensor_lamb_compute_update_term(8192, flag, [g16, p, m, v, u], *hp, step, eps, 1, wd, gs, gn, 1.0)
+                _, un = ref.multi_tensor_l2norm(65536, flag, [u], True)
+                dl.multi_tensor_lamb_update_weights(8192, flag, [u, p, p16], pn, un, off, lr, wd, gn, False)
+            ms, host = timeit(ref_step, args.iters)
+            report("C6 sharded LAMB, 336M-param shard", "l2norm(p16) + stage1 + l2norm(u) + stage2 (46 B/param)", "reference_cuda",
+                   ms, host, 46 * P, P)
+            fn = lambda: dl.multi_tensor_lamb_compute_update_term(8192, flag, [g16, p, m, v, u], *hp, step, eps, 1, wd, gs, gn, 1.0)
+            ms, host = timeit(fn, args.iters)
+            report("C6 sharded LAMB, 336M-param shard", "stage1 (26 B/param)", "reference_cuda", ms, host, 26 * P, P)
+            fn = lambda: dl.multi_tensor_lamb_update_weights(8192, flag, [u, p, p16], n2[0], n2[1], off, lr, wd, gn, False)
+            ms, host = timeit(fn, args.iters)
+            report("C6 sharded LAMB, 336M-param shard", "stage2 (14 B/param)", "reference_cuda", ms, host, 14 * P, P)
+
 
 if __name__ == "__main__":
     main()
