@@ -70,3 +70,58 @@ def allreduce_bucket(bucket: Sequence[torch.Tensor], process_group=None, gradien
     """One-shot form with the reference's argument meaning (a fresh flat buffer per call)."""
     return FlatBucketAllreduce(bucket, process_group, gradient_average, gradient_predivide_factor,
                                allreduce_always_fp32)()
+
+
+# ---- apex_C.flatten / unflatten and the flat_dist_call helpers (apex/parallel/distributed.py:13-76) -------------------
+def _amp_scale():
+    from .. import load_amp_C
+
+    return load_amp_C().multi_tensor_scale
+
+
+def flatten(bucket: Sequence[torch.Tensor]) -> torch.Tensor:
+    """One contiguous 1-D tensor holding the bucket's tensors back to back (csrc/flatten_unflatten.cpp:5-8), written by
+    ONE multi_tensor_scale launch instead of one copy kernel per tensor."""
+    bucket = list(bucket)
+    flat = torch.empty(sum(t.numel() for t in bucket), dtype=bucket[0].dtype, device=bucket[0].device)
+    if flat.numel():
+        flag = torch.zeros(1, dtype=torch.int32, device=flat.device)
+        multi_tensor_applier(_amp_scale(), flag, [[t.reshape(-1) for t in bucket], list(_views(flat, bucket))], 1.0)
+    return flat
+
+
+def _views(flat, like):
+    o = 0
+    for t in like:
+        yield flat[o:o + t.numel()]
+        o += t.numel()
+
+
+def unflatten(coalesced: torch.Tensor, bucket: Sequence[torch.Tensor]):
+    """Views of `coalesced` shaped like the bucket's tensors (csrc/flatten_unflatten.cpp:10-13)."""
+    return [v.view(t.shape) for v, t in zip(_views(coalesced, bucket), bucket)]
+
+
+def apply_flat_dist_call(bucket, call, extra_args=None):
+    """flatten -> call(coalesced, *extra_args) -> (average if call is all_reduce) -> copy back (:36-49).  The average
+    rides on the copy back, which is one launch."""
+    bucket = list(bucket)
+    coalesced = flatten(bucket)
+    call(coalesced, *(extra_args or ()))
+    post = 1.0 / dist.get_world_size() if call is dist.all_reduce else 1.0
+    flag = torch.zeros(1, dtype=torch.int32, device=coalesced.device)
+    multi_tensor_applier(_amp_scale(), flag, [list(_views(coalesced, bucket)), [t.reshape(-1) for t in bucket]], post)
+
+
+def split_by_type(tensors):
+    buckets = {}
+    for t in tensors:
+        buckets.setdefault(t.type(), []).append(t)
+    return buckets
+
+
+def flat_dist_call(tensors, call, extra_args=None):
+    """Organise `tensors` by type and run `call` on each type's flattened bucket (:68-73): how the reference's
+    DistributedDataParallel broadcasts the parameters from rank 0 at construction (:252)."""
+    for bucket in split_by_type(tensors).values():
+        apply_flat_dist_call(bucket, call, extra_args)

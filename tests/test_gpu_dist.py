@@ -206,6 +206,18 @@ def _bucket_worker(rank, world, port, outdir):
             bucket[1][0] = float("inf")
             red()
             out[str(dt) + "_flag"] = int(red.overflow_buf.item())
+        # flat_dist_call: broadcast mixed-dtype "parameters" from rank 0, then an averaging all_reduce
+        from beforeholiday_b200.parallel import flat_dist_call, flatten, unflatten
+
+        ps = [torch.full((n,), float(rank + 1), device=dev, dtype=dt) for n, dt in
+              ((5, torch.float32), (70001, torch.float16), (33, torch.float32), (4096, torch.bfloat16))]
+        flat_dist_call(ps, dist.broadcast, (0,))
+        out["broadcast"] = all(bool((p == 1).all()) for p in ps)
+        gs = [torch.full((n,), float(rank), device=dev) for n in (7, 9000)]
+        flat_dist_call(gs, dist.all_reduce)
+        out["allreduce_avg"] = all(bool((g == (world - 1) / 2).all()) for g in gs)
+        f = flatten(gs)
+        out["flatten"] = f.numel() == 9007 and all(v.data_ptr() == f.data_ptr() + 4 * o for v, o in zip(unflatten(f, gs), (0, 7)))
         torch.save(out, os.path.join(outdir, f"rank{rank}.pt"))
     finally:
         dist.destroy_process_group()
