@@ -312,6 +312,15 @@ def main():
         f"{achieved / 8000 * 100:.1f}% of 8 TB/s nominal); per-step ms min/max {min(per_step):.3f}/{max(per_step):.3f}")
 
     traffic = ncu_traffic()
+    traffic_bytes = traffic_src = None
+    if traffic:
+        if traffic.get("captured_workload") == args.workload and traffic.get("captured_params") == P:
+            traffic_bytes = traffic["dram_bytes_per_launch"]      # measured on this very launch
+            traffic_src = f"ncu dram__bytes_read.sum + dram__bytes_write.sum of this launch ({traffic['source']})"
+        else:
+            traffic_bytes = BYTES_PER_PARAM * P * traffic["traffic_over_algorithmic"]
+            traffic_src = (f"ncu dram bytes / algorithmic bytes = {traffic['traffic_over_algorithmic']} measured on "
+                           f"{traffic['captured_workload']} ({traffic['source']}), scaled to this launch")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -321,10 +330,7 @@ def main():
                    "bytes_per_param": BYTES_PER_PARAM, "l2": "inputs (16 B/param resident) are >> L2; no flush needed",
                    "hyper": HP},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": (BYTES_PER_PARAM * P * traffic["traffic_over_algorithmic"]) if traffic else None,
-                     "traffic_source": (f"ncu dram bytes / algorithmic bytes = {traffic['traffic_over_algorithmic']} measured on "
-                                        f"{traffic['captured_workload']} ({traffic['source']}), scaled to this launch")
-                     if traffic else None,
+                     "traffic": traffic_bytes, "traffic_source": traffic_src,
                      "peak_source": peak_src,
                      "frac_of_8TBps_nominal": achieved / 8000.0, "kernel": "mt_table_kernel<DistAdamOp<bf16,copy,noop>>",
                      "algorithmic_bytes_per_launch": BYTES_PER_PARAM * P},
