@@ -126,7 +126,6 @@ class DistributedFusedAdam:
         self.params = params
         self.device = torch.device(device if device is not None else "cuda")
         self.grad_dtype, self.param_dtype = grad_dtype, param_dtype
-        assert grad_dtype == param_dtype or params is None or True
         self.lr, self.betas, self.eps = lr, betas, eps
         self.bias_correction, self.adam_w_mode, self.weight_decay = bias_correction, adam_w_mode, weight_decay
         self.average_grad_sync = average_grad_sync
