@@ -259,3 +259,37 @@ def test_bert_large_lamb_full_oracle(amp_C, oracle, use_nvlamb):
     for i in (0, 5, nt - 1):
         r = float(torch.linalg.vector_norm(host[0][i], dtype=torch.float64))
         assert abs(float(un[i]) - r) <= 1e-5 * r
+
+
+# ------------------------------------------------------------------------------------------------ C1: 1 M-param MLP
+@pytest.mark.parametrize("adam_w_mode,wd", [(False, 0.0), (True, 0.01)])
+def test_c1_mlp_fused_adam_vs_torch_optim_cpu(adam_w_mode, wd):
+    """C1: the ~1 M-parameter fp32 MLP (986 634 params, 6 tensors) trained for 7 steps with FusedAdam on the B200 against
+    torch.optim.Adam / AdamW on the CPU fed the very same gradient bits (the reference's own CPU-runnable oracle,
+    tests/L0/run_optimizers/test_fused_optimizer.py:64-88).  Tolerance 1e-6 relative (north star), and the reference
+    test's 1e-3 absolute."""
+    from beforeholiday_b200.optimizers import FusedAdam
+
+    torch.manual_seed(9876)
+    mk = lambda: torch.nn.Sequential(torch.nn.Linear(1024, 768), torch.nn.ReLU(), torch.nn.Linear(768, 256), torch.nn.ReLU(),
+                                     torch.nn.Linear(256, 10))
+    cpu_model = mk()
+    gpu_model = mk().cuda()
+    gpu_model.load_state_dict(cpu_model.state_dict())
+    assert sum(p.numel() for p in cpu_model.parameters()) == 986634
+    opts = dict(lr=5e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=wd)
+    ref = (torch.optim.AdamW if adam_w_mode else torch.optim.Adam)(cpu_model.parameters(), **opts)
+    tst = FusedAdam(gpu_model.parameters(), adam_w_mode=adam_w_mode, **opts)
+    for it in range(7):
+        x = torch.randn(64, 1024, device="cuda")
+        y = torch.randint(0, 10, (64,), device="cuda")
+        tst.zero_grad()
+        torch.nn.functional.cross_entropy(gpu_model(x), y).backward()
+        for pc, pg in zip(cpu_model.parameters(), gpu_model.parameters()):
+            pc.grad = pg.grad.detach().cpu().clone()
+        tst.step()
+        ref.step()
+    for pc, pg in zip(cpu_model.parameters(), gpu_model.parameters()):
+        a, b = pg.detach().cpu(), pc.detach()
+        assert float((a - b).abs().max()) <= 1e-3
+        assert torch.allclose(a, b, rtol=1e-6, atol=2e-7)
