@@ -115,3 +115,10 @@ def stream_ptr(device=None):
 
 def vp(t):
     return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def cache_stats(device: int = 0) -> dict:
+    """Counters of the device tensor-table cache (hits, misses, uploads_bytes, entries, device_bytes)."""
+    st = MtCacheStats()
+    check(lib().mt_table_cache_stats(int(device), C.byref(st)))
+    return {n: int(getattr(st, n)) for n, _ in MtCacheStats._fields_}

@@ -75,6 +75,7 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     using namespace mt;
     const char* who = "multi_tensor_l2norm_noalloc";
     int rc = validate_lists(tl, 1, 1, who);
+    if (!rc) rc = validate_entries(tl, who);
     if (rc) return rc;
     if (chunk_size <= 0) return set_error(MT_EINVAL, "%s: chunk_size must be positive", who);
     if (!noop_flag || !ret) return set_error(MT_EINVAL, "%s: noop_flag / ret is NULL", who);

@@ -44,7 +44,8 @@ int device_info(int device, DeviceInfo* out);
 // ---- validation ---------------------------------------------------------------------------------
 // Mirrors the checks of /root/reference/csrc/multi_tensor_apply.cuh:53-72 that survive the loss of
 // torch types (depth, list lengths and numel equality are structural in MtTensorLists).
-int validate_lists(const MtTensorLists* tl, int expect_depth_lo, int expect_depth_hi, const char* who);
+int validate_lists(const MtTensorLists* tl, int expect_depth_lo, int expect_depth_hi, const char* who);  // O(1)
+int validate_entries(const MtTensorLists* tl, const char* who);  // O(ntensors): negative numel, NULL pointers
 int64_t total_elems(const MtTensorLists* tl);
 
 // ---- tiles ----------------------------------------------------------------------------------------

@@ -55,6 +55,12 @@ int validate_lists(const MtTensorLists* tl, int lo, int hi, const char* who) {
     for (int d = 0; d < tl->depth; d++)
         if (tl->dtype[d] < MT_F32 || tl->dtype[d] > MT_F64)
             return set_error(MT_EINVAL, "%s: list %d has unknown dtype tag %d", who, d, tl->dtype[d]);
+    return MT_OK;
+}
+
+// Per-entry checks.  O(ntensors x depth): run when a table is BUILT (a pointer set that hits the cache was checked when
+// it was inserted), and by callers that build their own table.
+int validate_entries(const MtTensorLists* tl, const char* who) {
     for (int64_t t = 0; t < tl->ntensors; t++) {
         if (tl->numel[t] < 0) return set_error(MT_EINVAL, "%s: tensor %lld has negative numel", who, (long long)t);
         if (tl->numel[t] > 0)
@@ -79,8 +85,10 @@ uint64_t count_tiles(const MtTensorLists* tl, int tile_elems) {
 
 int choose_tile_elems(const MtTensorLists* tl, int device) {
     // MT_TILE_ELEMS: tuning override (multiple of 2048)
-    const char* forced_env = getenv("MT_TILE_ELEMS");
-    const int forced = forced_env ? atoi(forced_env) : 0;
+    static const int forced = [] {
+        const char* e = getenv("MT_TILE_ELEMS");
+        return e ? atoi(e) : 0;
+    }();
     if (forced >= kRound && forced % kRound == 0) return forced;
     DeviceInfo di;
     if (device_info(device, &di) != MT_OK || di.sms <= 0) di.sms = 148;
@@ -93,6 +101,7 @@ int choose_tile_elems(const MtTensorLists* tl, int device) {
         cnt[0] += (n + 16383) >> 14;
         cnt[1] += (n + 8191) >> 13;
         cnt[2] += (n + 4095) >> 12;
+        if (cnt[0] >= want) return 16384;  // the common case ends after a few tensors
     }
     static_assert(kMaxTile == 16384 && kRound == 2048, "candidate tile sizes are hard-wired below");
     if (cnt[0] >= want) return 16384;
@@ -115,6 +124,13 @@ struct Entry {
 struct DeviceCache {
     std::mutex mu;
     std::unordered_multimap<uint64_t, Entry> map;
+    // Most-recently-used entries, checked before anything is hashed: a training loop cycles through a handful of
+    // (op, lists) pairs, and comparing the caller's pointer / numel arrays straight against a cached blob is one
+    // memcmp pass instead of blob build (a 64-bit division per tensor) + hash + memcmp.  Pointers into `map` nodes
+    // (stable until erased; cleared on eviction).
+    static constexpr int kMru = 16;
+    Entry* mru[kMru] = {};
+    int mru_n = 0;
     void* staging = nullptr;  // pinned
     size_t staging_cap = 0;
     cudaEvent_t staging_ev = nullptr;
@@ -167,8 +183,32 @@ int evict_all_locked(DeviceCache& c) {
         c.stats.device_bytes -= it->second.bytes;
         it = c.map.erase(it);
     }
+    c.mru_n = 0;
     c.stats.entries = c.map.size();
     return MT_OK;
+}
+
+inline void mru_touch(DeviceCache& c, Entry* e) {
+    int pos = c.mru_n;
+    for (int i = 0; i < c.mru_n; i++)
+        if (c.mru[i] == e) { pos = i; break; }
+    if (pos == c.mru_n) {
+        if (c.mru_n < DeviceCache::kMru) c.mru_n++;
+        pos = c.mru_n - 1;
+    }
+    for (int i = pos; i > 0; i--) c.mru[i] = c.mru[i - 1];
+    c.mru[0] = e;
+}
+
+inline void fill_out(const Entry* e, size_t nt, int tile_elems, size_t off_tb, size_t off_numel, size_t off_ptrs,
+                     DevTable* out) {
+    const uint8_t* d = static_cast<const uint8_t*>(e->dev);
+    out->tile_begin = reinterpret_cast<const uint32_t*>(d + off_tb);
+    out->numel = reinterpret_cast<const int64_t*>(d + off_numel);
+    out->ptrs = reinterpret_cast<const void* const*>(d + off_ptrs);
+    out->ntensors = (int32_t)nt;
+    out->ntiles = e->ntiles;
+    out->tile_elems = tile_elems;
 }
 
 }  // namespace
@@ -189,6 +229,32 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
     const size_t off_ptrs = off_numel + nt * 8;
     const size_t bytes = off_ptrs + (size_t)depth * nt * 8;
 
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    MT_CUDA_OK(cudaStreamIsCapturing(stream, &cap));
+    const bool capturing = cap != cudaStreamCaptureStatusNone;
+    DeviceCache& c = g_cache[device];
+    {   // MRU fast path: no blob, no hash
+        std::lock_guard<std::mutex> lk(c.mu);
+        for (int i = 0; i < c.mru_n; i++) {
+            Entry* e = c.mru[i];
+            if (e->bytes != bytes) continue;
+            const uint8_t* hb = e->host.data();
+            const int32_t* hdr = reinterpret_cast<const int32_t*>(hb);
+            if (hdr[0] != depth || hdr[1] != tile_elems) continue;
+            if (memcmp(hb + off_ptrs, tl->ptrs, (size_t)depth * nt * 8) != 0) continue;
+            if (memcmp(hb + off_numel, tl->numel, nt * 8) != 0) continue;
+            c.stats.hits++;
+            if (capturing) e->in_graph = true;
+            if (i) mru_touch(c, e);
+            fill_out(e, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
+            return MT_OK;
+        }
+    }
+
+    {   // not seen recently: per-entry validation before anything is built from the arrays
+        const int vrc = validate_entries(tl, "tensor lists");
+        if (vrc) return vrc;
+    }
     thread_local std::vector<uint8_t> blob;
     blob.resize(bytes);
     memset(blob.data(), 0, off_tb);  // header padding; the arrays below are fully overwritten (plus their alignment gap)
@@ -210,11 +276,6 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
     const uint32_t ntiles = reinterpret_cast<uint32_t*>(blob.data() + off_tb)[nt];
     const uint64_t h = hash_blob(blob.data(), bytes);
 
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    MT_CUDA_OK(cudaStreamIsCapturing(stream, &cap));
-    const bool capturing = cap != cudaStreamCaptureStatusNone;
-
-    DeviceCache& c = g_cache[device];
     std::lock_guard<std::mutex> lk(c.mu);
     Entry* e = nullptr;
     auto range = c.map.equal_range(h);
@@ -269,13 +330,8 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
         c.stats.entries = c.map.size();
         e = &it->second;
     }
-    const uint8_t* d = static_cast<const uint8_t*>(e->dev);
-    out->tile_begin = reinterpret_cast<const uint32_t*>(d + off_tb);
-    out->numel = reinterpret_cast<const int64_t*>(d + off_numel);
-    out->ptrs = reinterpret_cast<const void* const*>(d + off_ptrs);
-    out->ntensors = (int32_t)nt;
-    out->ntiles = ntiles;
-    out->tile_elems = tile_elems;
+    mru_touch(c, e);
+    fill_out(e, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
     return MT_OK;
 }
 

@@ -256,3 +256,30 @@ def test_c_abi_direct_ctypes(oracle):
                                   C.c_size_t(4), _lib.stream_ptr())
     assert rc == -4 and b"scratch too small" in L.mt_last_error()
     assert L.mt_launch_count() - launches0 == 1 + 1 + 2
+
+
+def test_c_abi_rejects_bad_entries_then_serves_cached_sets():
+    """Per-entry validation (NULL pointer, negative numel) happens when a table is built; a set that is already cached
+    is served from the most-recently-used list without being re-walked."""
+    from beforeholiday_b200 import _lib
+
+    L = _lib.lib()
+    L.mt_last_error.restype = C.c_char_p
+    x = [rnd(5000, F32, 1), rnd(7, F32, 2)]
+    o = [torch.zeros(5000, device="cuda"), torch.zeros(7, device="cuda")]
+    f = flag()
+    tl = _lib.Lists([x, o])
+    tl.ptr_arr[3] = None                                    # list 1, tensor 1
+    rc = L.mt_multi_tensor_scale(8192, _lib.vp(f), tl.ref, C.c_float(1.0), _lib.stream_ptr())
+    assert rc != 0 and b"NULL pointer" in L.mt_last_error()
+    tl.ptr_arr[3] = o[1].data_ptr()
+    tl.numel_arr[0] = -5
+    rc = L.mt_multi_tensor_scale(8192, _lib.vp(f), tl.ref, C.c_float(1.0), _lib.stream_ptr())
+    assert rc != 0 and b"negative numel" in L.mt_last_error()
+    tl.numel_arr[0] = 5000
+    st0 = _lib.cache_stats(0)
+    for _ in range(3):
+        _lib.check(L.mt_multi_tensor_scale(8192, _lib.vp(f), tl.ref, C.c_float(2.0), _lib.stream_ptr()))
+    st1 = _lib.cache_stats(0)
+    assert st1["misses"] - st0["misses"] == 1 and st1["hits"] - st0["hits"] == 2
+    assert torch.equal(o[0], x[0] * 2) and torch.equal(o[1], x[1] * 2)

@@ -190,8 +190,27 @@ def main():
             report("C4 BERT-large 336M", "LAMB step incl. grad norm", name, ms, host, (44 if mod is mine else 52) * P, P,
                    launches_of(lamb_step) if mod is mine else None,
                    {"bytes_per_param": 44 if mod is mine else 52})
+        # the CPU step beside it (north star): the oracle's LAMB restatement (OpenMP, all host cores) on the same set
+        try:
+            import os
+
+            from oracle import mt_oracle as O
+
+            hl = [[t.cpu() for t in l] for l in (g, p, m, v)]
+            fl = torch.zeros(1, dtype=torch.int32)
+            best = 1e30
+            for _ in range(3):
+                t0 = time.perf_counter()
+                gn, _ = O.multi_tensor_l2norm(65536, fl, [hl[0]], False)
+                O.multi_tensor_lamb(8192, fl, hl, 5e-4, 0.9, 0.999, 1e-6, 3, 1, 0.01, 1, 1, gn, 1.0, False)
+                best = min(best, (time.perf_counter() - t0) * 1e3)
+            report("C4 BERT-large 336M", "LAMB step incl. grad norm", f"cpu_oracle_port x{O.lib().orc_num_threads()} threads "
+                   f"({os.cpu_count()} cores)", best, best, 52 * P, P)
+        except Exception as e:  # noqa: BLE001
+            print(json.dumps({"config": "C4", "cpu_oracle_error": repr(e)[:200]}), flush=True)
 
     if "c6" in cfgs:
+        flag.zero_()   # earlier configs may have raised it (uninitialised fp16 inputs); these kernels honour the flag
         # sharded LAMB kernels on a BERT-large-sized shard: fp16 grads and model copy, fp32 p/m/v/u
         shapes = workloads.bert_large()
         P = workloads.total(shapes)
