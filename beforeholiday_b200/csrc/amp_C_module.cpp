@@ -132,13 +132,29 @@ class WalkPool {
     uint64_t generation_ = 0;
 };
 
+// torch.nn.Parameter instances are THPVariable objects of a subclass type: same layout, no __torch_function__ games.
+// Optimizers pass lists of them, so they must stay on the fast path (an isinstance() check needs the Python API).
+PyTypeObject* g_parameter_type = nullptr;
+inline bool is_plain_tensor(PyObject* o) {
+    PyTypeObject* t = Py_TYPE(o);
+    return t == reinterpret_cast<PyTypeObject*>(THPVariableClass) || (g_parameter_type && t == g_parameter_type);
+}
+
 // One (list, tensor) entry: the reference's per-tensor checks (/root/reference/csrc/multi_tensor_apply.cuh:60-71).
 // Returns NULL or a static error message; never throws and never calls into Python, so it may run on worker threads.
 // *special is set for entries the fast path does not handle (tensor subclasses needing isinstance, sparse tensors).
 inline const char* check_entry(PyObject* item, const c10::Device& ref_device, at::ScalarType st0, bool first_list,
-                               int64_t* numel_slot, const void** ptr_slot, bool* special) {
-    if (!THPVariable_CheckExact(item)) { *special = true; return nullptr; }
-    const at::Tensor& x = THPVariable_Unpack(item);
+                               int64_t* numel_slot, const void** ptr_slot, bool* special, bool grad = false) {
+    if (!is_plain_tensor(item)) { *special = true; return nullptr; }
+    const at::Tensor& x0 = THPVariable_Unpack(item);
+    // grad = true: the entry is the .grad of the listed parameter (the optimizers' fast path: no Python-side list of
+    // gradients is ever built).  Reading autograd metadata is a pure read; safe on the worker threads.
+    const at::Tensor& x = grad ? x0.grad() : x0;
+    if (grad) {
+        if (!x.defined()) return "grads_of: a parameter has no gradient";
+        if (x.is_sparse()) return "grads_of: sparse gradient";
+        if (x.sizes() != x0.sizes() || x.strides() != x0.strides()) return "grads_of: gradient layout differs from its parameter";
+    }
     if (x.is_sparse()) { *special = true; return nullptr; }
     if (!x.is_contiguous() && !x.is_contiguous(at::MemoryFormat::ChannelsLast) &&
         !x.is_contiguous(at::MemoryFormat::ChannelsLast3d))
@@ -156,17 +172,34 @@ inline const char* check_entry(PyObject* item, const c10::Device& ref_device, at
 // directly: the reference's signature (std::vector<std::vector<at::Tensor>> by value) costs a type-cast plus a
 // reference-count round trip per tensor, which at 50k tensors x 3 lists is several milliseconds -- more than the
 // kernel itself on a B200.  Long lists are checked by a few worker threads (pure reads of tensor metadata).
-void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, const char* who, Flat& f) {
+// grads_of >= 0 (the optimizers' fast path): an extra list 0 is synthesised from the .grad of the tensors of given list
+// `grads_of`, so the caller never builds a Python list of gradients; with grads_only the given lists themselves are
+// dropped (norm of the gradients of a parameter list).  Any entry the fast path cannot take raises a RuntimeError whose
+// message starts with "grads_of:" -- the Python caller falls back to building the lists itself.
+void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, const char* who, Flat& f, int grads_of = -1,
+             bool grads_only = false) {
     FastSeq outer(lists_obj.ptr(), "tensor_lists must be a sequence of sequences of tensors");
-    const size_t depth = (size_t)outer.size();
+    const size_t given = (size_t)outer.size();
+    TORCH_CHECK(given >= 1, "tensor_lists.size() != depth");
+    TORCH_CHECK(grads_of < (int)given, "grads_of: list index out of range");
+    const size_t depth = grads_of < 0 ? given : (grads_only ? 1 : given + 1);
     TORCH_CHECK(depth >= depth_lo && depth <= depth_hi, "tensor_lists.size() != depth");
     std::vector<std::unique_ptr<FastSeq>> inner;
-    inner.reserve(depth);
-    for (size_t l = 0; l < depth; l++)
+    inner.reserve(given);
+    for (size_t l = 0; l < given; l++)
         inner.emplace_back(new FastSeq(outer[l], "tensor_lists must be a sequence of sequences of tensors"));
     const size_t len0 = (size_t)inner[0]->size();
     TORCH_CHECK(len0 > 0, "tensor_lists[0].size() is not > 0");
-    for (size_t l = 0; l < depth; l++) TORCH_CHECK((size_t)inner[l]->size() == len0, "Size mismatch among tensor lists");
+    for (size_t l = 0; l < given; l++) TORCH_CHECK((size_t)inner[l]->size() == len0, "Size mismatch among tensor lists");
+    // list sources: where list l's entries come from
+    struct Src { PyObject** items; bool grad; };
+    Src src[MT_MAX_DEPTH + 1];
+    {
+        size_t k = 0;
+        if (grads_of >= 0) src[k++] = Src{PySequence_Fast_ITEMS(inner[grads_of]->o), true};
+        if (!(grads_of >= 0 && grads_only))
+            for (size_t l = 0; l < given; l++) src[k++] = Src{PySequence_Fast_ITEMS(inner[l]->o), false};
+    }
     TORCH_CHECK(THPVariable_Check((*inner[0])[0]), who, ": tensor_lists must contain tensors");
     f.first = THPVariable_Unpack((*inner[0])[0]);
     const c10::Device ref_device = f.first.device();
@@ -175,29 +208,32 @@ void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, cons
     f.numel.assign(len0, 0);
     at::ScalarType st0[MT_MAX_DEPTH];
     for (size_t l = 0; l < depth; l++) {
-        PyObject* it0 = (*inner[l])[0];
+        PyObject* it0 = src[l].items[0];
         TORCH_CHECK(THPVariable_Check(it0), who, ": tensor_lists must contain tensors");
-        st0[l] = THPVariable_Unpack(it0).scalar_type();
+        const at::Tensor& x0 = THPVariable_Unpack(it0);
+        if (src[l].grad) TORCH_CHECK(x0.grad().defined(), "grads_of: a parameter has no gradient");
+        st0[l] = src[l].grad ? x0.grad().scalar_type() : x0.scalar_type();
         f.tl.dtype[l] = dtype_tag(st0[l], who);
     }
 
     // fast path over [t0, t1): list 0 first (it defines numel), then the others
     auto run_range = [&](size_t t0, size_t t1, const char** err, bool* special) {
         for (size_t l = 0; l < depth && !*err; l++) {
-            PyObject** items = PySequence_Fast_ITEMS(inner[l]->o);
+            PyObject** items = src[l].items;
+            const bool grad = src[l].grad;
             for (size_t t = t0; t < t1; t++) {
                 // The walk is bound by cache misses on objects scattered over the heap (PyObject -> TensorImpl ->
                 // StorageImpl, one dependent miss each): run three prefetch stages ahead of the checks.
                 if (t + 24 < t1) __builtin_prefetch(items[t + 24]);
-                if (t + 16 < t1 && THPVariable_CheckExact(items[t + 16])) {
+                if (t + 16 < t1 && is_plain_tensor(items[t + 16])) {
                     const char* impl = reinterpret_cast<const char*>(THPVariable_Unpack(items[t + 16]).unsafeGetTensorImpl());
                     __builtin_prefetch(impl);
                     __builtin_prefetch(impl + 64);
                     __builtin_prefetch(impl + 128);
                 }
-                if (t + 8 < t1 && THPVariable_CheckExact(items[t + 8]))
+                if (t + 8 < t1 && is_plain_tensor(items[t + 8]) && !grad)
                     __builtin_prefetch(THPVariable_Unpack(items[t + 8]).unsafeGetTensorImpl()->unsafe_storage().unsafeGetStorageImpl());
-                const char* e = check_entry(items[t], ref_device, st0[l], l == 0, &f.numel[t], &f.ptrs[l * len0 + t], special);
+                const char* e = check_entry(items[t], ref_device, st0[l], l == 0, &f.numel[t], &f.ptrs[l * len0 + t], special, grad);
                 if (e) { *err = e; break; }
             }
         }
@@ -227,6 +263,7 @@ void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, cons
     if (special) {
         // slow path (rare): tensor subclasses that need isinstance(), sparse tensors (densified as
         // multi_tensor_apply.cuh:92-95 does).  Serial, with the GIL, may allocate.
+        TORCH_CHECK(grads_of < 0, "grads_of: unsupported tensor kind (subclass or sparse) in the lists");
         err = nullptr;
         for (size_t l = 0; l < depth; l++)
             for (size_t t = 0; t < len0; t++) {
@@ -236,9 +273,9 @@ void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, cons
                 if (!x.is_sparse()) {
                     bool sp2 = false;
                     PyObject* exact = item;
-                    const char* e = THPVariable_CheckExact(exact)
+                    const char* e = is_plain_tensor(exact)
                         ? check_entry(item, ref_device, st0[l], l == 0, &f.numel[t], &f.ptrs[l * len0 + t], &sp2) : nullptr;
-                    if (!THPVariable_CheckExact(exact)) {  // subclass: same checks through the Tensor API
+                    if (!is_plain_tensor(exact)) {  // subclass: same checks through the Tensor API
                         bool cm = x.is_contiguous() || x.is_contiguous(at::MemoryFormat::ChannelsLast) ||
                                   x.is_contiguous(at::MemoryFormat::ChannelsLast3d);
                         TORCH_CHECK(cm, "A tensor was not contiguous.");
@@ -294,10 +331,11 @@ void multi_tensor_axpby(int chunk_size, at::Tensor noop_flag, TensorLists tensor
 
 std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_flag, const py::object& tensor_lists,
                                                bool with_scale, float scale, at::optional<bool> per_tensor_python,
-                                               bool mp = false) {
+                                               bool mp = false, int grads_of = -1) {
     const bool per_tensor = per_tensor_python.has_value() ? per_tensor_python.value() : false;
     Flat f;
-    flatten(tensor_lists, with_scale ? 2 : 1, with_scale ? 2 : 1, with_scale ? "multi_tensor_l2norm_scale" : "multi_tensor_l2norm", f);
+    flatten(tensor_lists, with_scale ? 2 : 1, with_scale ? 2 : 1, with_scale ? "multi_tensor_l2norm_scale" : "multi_tensor_l2norm", f,
+            grads_of, /*grads_only=*/grads_of >= 0);
     const c10::cuda::CUDAGuard guard(f.device);
     auto fopt = f.first.options().dtype(at::kFloat).layout(at::kStrided);
     at::Tensor ret = at::empty({1}, fopt);
@@ -321,9 +359,10 @@ std::tuple<at::Tensor, at::Tensor> l2norm_impl(int chunk_size, at::Tensor noop_f
     return std::make_tuple(ret, ret_per_tensor);
 }
 
+// grads_of (extension, default -1): norm of the GRADIENTS of the parameters in tensor_lists[grads_of]
 std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists,
-                                                       at::optional<bool> per_tensor_python) {
-    return l2norm_impl(chunk_size, noop_flag, tensor_lists, false, 0.f, per_tensor_python);
+                                                       at::optional<bool> per_tensor_python, int grads_of) {
+    return l2norm_impl(chunk_size, noop_flag, tensor_lists, false, 0.f, per_tensor_python, false, grads_of);
 }
 
 std::tuple<at::Tensor, at::Tensor> multi_tensor_l2norm_scale(int chunk_size, at::Tensor noop_flag,
@@ -360,17 +399,18 @@ void multi_tensor_lamb_mp(int chunk_size, at::Tensor noop_flag, TensorLists tens
 
 void multi_tensor_adam(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
                        const float beta1, const float beta2, const float epsilon, const int step, const int mode,
-                       const int bias_correction, const float weight_decay) {
+                       const int bias_correction, const float weight_decay, int grads_of) {
     Flat f;
-    flatten(tensor_lists, 4, 4, "multi_tensor_adam", f);
+    flatten(tensor_lists, 4, 4, "multi_tensor_adam", f, grads_of);
     check(mt_multi_tensor_adam(chunk_size, flag_ptr(noop_flag), &f.tl, lr, beta1, beta2, epsilon, step, mode,
                                bias_correction, weight_decay, f.stream));
 }
 
 void multi_tensor_sgd(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, float wd, float momentum,
-                      float dampening, float lr, bool nesterov, bool first_run, bool wd_after_momentum, float scale) {
+                      float dampening, float lr, bool nesterov, bool first_run, bool wd_after_momentum, float scale,
+                      int grads_of) {
     Flat f;
-    flatten(tensor_lists, 3, 4, "multi_tensor_sgd", f);
+    flatten(tensor_lists, 3, 4, "multi_tensor_sgd", f, grads_of);
     if (f.tl.depth == 4) TORCH_CHECK(f.tl.dtype[3] == MT_F16, "Additional output tensors should always be fp16.");
     TORCH_CHECK(noop_flag.device() == f.first.device(),
                 "expected noop flag to be on the same device as tensors");
@@ -381,10 +421,11 @@ void multi_tensor_sgd(int chunk_size, at::Tensor noop_flag, TensorLists tensor_l
 void multi_tensor_lamb(int chunk_size, at::Tensor noop_flag, TensorLists tensor_lists, const float lr,
                        const float beta1, const float beta2, const float epsilon, const int step,
                        const int bias_correction, const float weight_decay, const int grad_averaging, const int mode,
-                       at::Tensor global_grad_norm, const float max_grad_norm, at::optional<bool> use_nvlamb_python) {
+                       at::Tensor global_grad_norm, const float max_grad_norm, at::optional<bool> use_nvlamb_python,
+                       int grads_of) {
     const bool use_nvlamb = use_nvlamb_python.has_value() ? use_nvlamb_python.value() : false;
     Flat f;
-    flatten(tensor_lists, 4, 4, "multi_tensor_lamb", f);
+    flatten(tensor_lists, 4, 4, "multi_tensor_lamb", f, grads_of);
     TORCH_CHECK(global_grad_norm.is_cuda() && global_grad_norm.scalar_type() == at::ScalarType::Float,
                 "global_grad_norm must be a CUDA float tensor");
     const c10::cuda::CUDAGuard guard(f.device);
@@ -628,9 +669,9 @@ py::dict table_cache_stats(int device) {
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.doc() = "B200-native amp_C: multi-tensor-apply optimizer path over libmt_b200.so";
     m.def("multi_tensor_scale", &multi_tensor_scale, "Fused overflow check + scale for a list of contiguous tensors");
-    m.def("multi_tensor_sgd", &multi_tensor_sgd, "Fused SGD optimizer for list of contiguous tensors");
+    m.def("multi_tensor_sgd", &multi_tensor_sgd, "Fused SGD optimizer for list of contiguous tensors", py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("wd"), py::arg("momentum"), py::arg("dampening"), py::arg("lr"), py::arg("nesterov"), py::arg("first_run"), py::arg("wd_after_momentum"), py::arg("scale"), py::arg("grads_of") = -1);
     m.def("multi_tensor_axpby", &multi_tensor_axpby, "out = a*x + b*y for a list of contiguous tensors");
-    m.def("multi_tensor_l2norm", &multi_tensor_l2norm, "Computes L2 norm for a list of contiguous tensors");
+    m.def("multi_tensor_l2norm", &multi_tensor_l2norm, "Computes L2 norm for a list of contiguous tensors", py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("per_tensor") = py::none(), py::arg("grads_of") = -1);
     m.def("multi_tensor_l2norm_mp", &multi_tensor_l2norm_mp, "Computes L2 norm for a list of contiguous tensors");
     m.def("multi_tensor_lamb_mp", &multi_tensor_lamb_mp, "Computes and apply update for LAMB optimizer");
     m.def("multi_tensor_l2norm_scale", &multi_tensor_l2norm_scale,
@@ -638,8 +679,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("multi_tensor_lamb_stage1_cuda", &multi_tensor_lamb_stage1_cuda, "Computes update part of LAMB optimizer");
     m.def("multi_tensor_lamb_stage2_cuda", &multi_tensor_lamb_stage2_cuda,
           "Completes application of gradient to parameters for LAMB optimizer");
-    m.def("multi_tensor_adam", &multi_tensor_adam, "Compute and apply gradient update to parameters for Adam optimizer");
-    m.def("multi_tensor_lamb", &multi_tensor_lamb, "Computes and apply update for LAMB optimizer");
+    m.def("multi_tensor_adam", &multi_tensor_adam, "Compute and apply gradient update to parameters for Adam optimizer", py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("lr"), py::arg("beta1"), py::arg("beta2"), py::arg("epsilon"), py::arg("step"), py::arg("mode"), py::arg("bias_correction"), py::arg("weight_decay"), py::arg("grads_of") = -1);
+    m.def("multi_tensor_lamb", &multi_tensor_lamb, "Computes and apply update for LAMB optimizer", py::arg("chunk_size"), py::arg("noop_flag"), py::arg("tensor_lists"), py::arg("lr"), py::arg("beta1"), py::arg("beta2"), py::arg("epsilon"), py::arg("step"), py::arg("bias_correction"), py::arg("weight_decay"), py::arg("grad_averaging"), py::arg("mode"), py::arg("global_grad_norm"), py::arg("max_grad_norm"), py::arg("use_nvlamb") = py::none(), py::arg("grads_of") = -1);
     m.def("multi_tensor_adagrad", &multi_tensor_adagrad, "Compute and apply gradient update to parameters for Adagrad optimizer");
     m.def("multi_tensor_novograd", &multi_tensor_novograd, "Compute and apply gradient update to parameters for NovoGrad optimizer");
     m.def("multi_tensor_lars", &multi_tensor_lars, "Fused LARS optimizer for list of contiguous tensors");
@@ -666,6 +707,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("global_grad_norm"), py::arg("max_grad_norm"), py::arg("seg_begin") = py::none(),
           py::arg("model_dtype") = py::none());
     m.def("multi_tensor_lamb_update_weights", &multi_tensor_lamb_update_weights, "Sharded LAMB stage 2: weight update");
+    {
+        py::object param_cls = py::module_::import("torch.nn.parameter").attr("Parameter");
+        g_parameter_type = reinterpret_cast<PyTypeObject*>(param_cls.release().ptr());  // kept for the life of the process
+    }
     m.def("_flatten_only", [](py::object lists) { Flat f; flatten(lists, 1, MT_MAX_DEPTH, "_flatten_only", f); return f.tl.ntensors; },
           "host-path profiling aid: validate + flatten the lists, launch nothing");
     m.def("launch_count", []() { return mt_launch_count(); }, "kernels launched by libmt_b200.so since load");

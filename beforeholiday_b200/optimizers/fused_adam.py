@@ -26,6 +26,7 @@ from __future__ import annotations
 import torch
 
 from ..multi_tensor_apply import multi_tensor_applier
+from ._fast_path import FastGroups, is_fallback
 
 
 class FusedAdam(torch.optim.Optimizer):
@@ -51,6 +52,7 @@ class FusedAdam(torch.optim.Optimizer):
         self.multi_tensor_fused_adam = amp_C.multi_tensor_fused_adam
         self.multi_tensor_fused_adam_capturable = amp_C.multi_tensor_fused_adam_capturable
         self._hp_cache = {}
+        self._fast = FastGroups()
         if self.capturable or self.master_weights:
             for group in self.param_groups:
                 if not self.adam_w_mode and group['weight_decay'] != 0:
@@ -61,6 +63,55 @@ class FusedAdam(torch.optim.Optimizer):
                 group['lr'] = torch.as_tensor(group['lr'], dtype=torch.float32).reshape(1).to(dev)
                 group['step'] = torch.zeros(1, dtype=torch.int32, device=dev)
             self._one = torch.ones(1, dtype=torch.float32, device=dev)
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        self._fast = FastGroups()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._fast.clear()       # exp_avg / exp_avg_sq are new tensors
+
+    def add_param_group(self, param_group):
+        super().add_param_group(param_group)
+        if hasattr(self, "_fast"):
+            self._fast.clear()
+
+    def _fast_step(self, gid, group, bias_correction, beta1, beta2):
+        """Steady-state path of the plain route (see _fast_path.py).  Returns the dtypes it has updated."""
+        def build(params):
+            dts = (torch.float16, torch.bfloat16, torch.float32)
+            if any(p.dtype not in dts for p in params):
+                return None
+            sets = []
+            for dt in dts:
+                sel = [p for p in params if p.dtype == dt]
+                if not sel:
+                    continue
+                for p in sel:
+                    state = self.state[p]
+                    if len(state) == 0:
+                        state['exp_avg'] = torch.zeros_like(p.data)
+                        state['exp_avg_sq'] = torch.zeros_like(p.data)
+                sets.append({'dtype': dt, 'params': sel, 'm': [self.state[p]['exp_avg'] for p in sel],
+                             'v': [self.state[p]['exp_avg_sq'] for p in sel]})
+            return sets
+
+        c = self._fast.get(gid, group, build)
+        done = []
+        if c is None:
+            return done
+        for st in c['sets']:
+            try:
+                self.multi_tensor_adam(multi_tensor_applier.chunk_size, self._dummy_overflow_buf,
+                                       [st['params'], st['m'], st['v']], group['lr'], beta1, beta2, group['eps'],
+                                       group['step'], self.adam_w_mode, bias_correction, group['weight_decay'], grads_of=0)
+            except RuntimeError as e:
+                if not is_fallback(e):
+                    raise
+                return done
+            done.append(st['dtype'])
+        return done
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -144,16 +195,19 @@ class FusedAdam(torch.optim.Optimizer):
             self._step_mixed(inv_scale, found_inf)
             return loss
 
-        for group in self.param_groups:
+        for gid, group in enumerate(self.param_groups):
             bias_correction = 1 if group['bias_correction'] else 0
             beta1, beta2 = group['betas']
             # one step counter per group, as the reference (fused_adam.py:111-114)
             group['step'] = group.get('step', 0) + 1
 
+            done = self._fast_step(gid, group, bias_correction, beta1, beta2)
+            if done and len(done) == len(self._fast._cache[gid]['sets']):
+                continue
             buckets = {torch.float16: ([], [], [], []), torch.bfloat16: ([], [], [], []),
                        torch.float32: ([], [], [], [])}
             for p in group['params']:
-                if p.grad is None:
+                if p.grad is None or p.dtype in done:
                     continue
                 if p.grad.data.is_sparse:
                     raise RuntimeError('FusedAdam does not support sparse gradients, please consider SparseAdam instead')

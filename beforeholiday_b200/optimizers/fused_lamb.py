@@ -12,6 +12,7 @@ from __future__ import annotations
 import torch
 
 from ..multi_tensor_apply import multi_tensor_applier, multi_tensor_applier_l2norm
+from ._fast_path import FastGroups, is_fallback
 
 
 class FusedLAMB(torch.optim.Optimizer):
@@ -35,6 +36,7 @@ class FusedLAMB(torch.optim.Optimizer):
         self.adam_w_mode = 1 if adam_w_mode else 0
         self.set_grad_none = set_grad_none
         self.use_nvlamb = use_nvlamb
+        self._fast = FastGroups()
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -43,6 +45,83 @@ class FusedLAMB(torch.optim.Optimizer):
                     p.grad = None
         else:
             super().zero_grad(set_to_none=False)
+
+    def __setstate__(self, state):
+        super().__setstate__(state)
+        self._fast = FastGroups()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._fast.clear()
+
+    def add_param_group(self, param_group):
+        super().add_param_group(param_group)
+        if hasattr(self, "_fast"):
+            self._fast.clear()
+
+    def _fast_sets(self):
+        """Cached per-group launch sets (see _fast_path.py), or None when any group cannot use the fast path."""
+        def build(params):
+            dts = (torch.float16, torch.float32)
+            if any(p.dtype not in dts for p in params):
+                return None
+            sets = []
+            for dt in dts:
+                sel = [p for p in params if p.dtype == dt]
+                if not sel:
+                    continue
+                for p in sel:
+                    state = self.state[p]
+                    if len(state) == 0:
+                        state['exp_avg'] = torch.zeros_like(p.data)
+                        state['exp_avg_sq'] = torch.zeros_like(p.data)
+                sets.append({'dtype': dt, 'params': sel, 'm': [self.state[p]['exp_avg'] for p in sel],
+                             'v': [self.state[p]['exp_avg_sq'] for p in sel]})
+            return sets
+
+        out = []
+        for gid, group in enumerate(self.param_groups):
+            c = self._fast.get(gid, group, build)
+            if c is None:
+                return None
+            out.append(c['sets'])
+        return out
+
+    def _fast_step(self):
+        """Whole step on the fast path: both norm sweeps and every lamb call read the gradients through `grads_of`.
+        Returns False (nothing launched that modifies state) when the generic path must run instead."""
+        all_sets = self._fast_sets()
+        if all_sets is None:
+            return False
+        flag = self._dummy_overflow_buf
+        device = self.param_groups[0]["params"][0].device
+        key = tuple(id(sets) for sets in all_sets)      # the cached per-group set lists are rebuilt as new objects
+        if getattr(self, '_fast_norm_lists', (None,))[0] != key:
+            p32 = [p for sets in all_sets for st in sets if st['dtype'] == torch.float32 for p in st['params']]
+            p16 = [p for sets in all_sets for st in sets if st['dtype'] == torch.float16 for p in st['params']]
+            self._fast_norm_lists = (key, p32, p16, all_sets)
+        _, p32, p16, _ = self._fast_norm_lists
+        try:
+            n32 = self.multi_tensor_l2norm(65536, flag, [p32], False, grads_of=0)[0] if p32 else torch.zeros(1, device=device)
+            n16 = self.multi_tensor_l2norm(65536, flag, [p16], False, grads_of=0)[0] if p16 else torch.zeros(1, device=device)
+        except RuntimeError as e:
+            if not is_fallback(e):
+                raise
+            return False            # norms only read: nothing to undo
+        global_grad_norm = self.multi_tensor_l2norm(65536, flag, [[n32, n16]], False)[0]
+        max_grad_norm = self.defaults['max_grad_norm']
+        for group, sets in zip(self.param_groups, all_sets):
+            bias_correction = 1 if group['bias_correction'] else 0
+            beta1, beta2 = group['betas']
+            grad_averaging = 1 if group['grad_averaging'] else 0
+            group['step'] = group.get('step', 0) + 1
+            for st in sets:
+                # the same gradients passed the grads_of checks a moment ago (norm sweep): this cannot fall back
+                self.multi_tensor_lamb(multi_tensor_applier.chunk_size, flag, [st['params'], st['m'], st['v']], group['lr'],
+                                       beta1, beta2, group['eps'], group['step'], bias_correction, group['weight_decay'],
+                                       grad_averaging, self.adam_w_mode, global_grad_norm, max_grad_norm, self.use_nvlamb,
+                                       grads_of=0)
+        return True
 
     def _global_grad_norm(self):
         g32, g16 = [], []
@@ -71,6 +150,8 @@ class FusedLAMB(torch.optim.Optimizer):
         if closure is not None:
             loss = closure()
 
+        if self._fast_step():
+            return loss
         global_grad_norm = self._global_grad_norm()
         max_grad_norm = self.defaults['max_grad_norm']
 

@@ -12,6 +12,7 @@ import torch
 from torch.optim.optimizer import required
 
 from ..multi_tensor_apply import multi_tensor_applier
+from ._fast_path import FastGroups, is_fallback
 
 
 def _grad_in_param_layout(p, grad=None):
@@ -54,11 +55,54 @@ class FusedSGD(torch.optim.Optimizer):
         self._dummy_overflow_buf = torch.tensor([0], dtype=torch.int,
                                                 device=self.param_groups[0]["params"][0].device)
         self.multi_tensor_sgd = load_amp_C().multi_tensor_sgd
+        self._fast = FastGroups()
 
     def __setstate__(self, state):
         super().__setstate__(state)
         for group in self.param_groups:
             group.setdefault('nesterov', False)
+        self._fast = FastGroups()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._fast.clear()       # the momentum buffers are new tensors
+
+    def add_param_group(self, param_group):
+        super().add_param_group(param_group)
+        if hasattr(self, "_fast"):
+            self._fast.clear()
+
+    def _fast_step(self, gid, group):
+        """Steady-state path (see _fast_path.py): cached parameter / momentum lists, gradients read by the extension.
+        Returns the dtypes it has updated; the generic path handles the rest (normally: everything or nothing)."""
+        def build(params):
+            by_dt = [(dt, [p for p in params if p.dtype == dt]) for dt in (torch.float16, torch.float32)]
+            if sum(len(sel) for _, sel in by_dt) != len(params):
+                return None                       # other dtypes present: the generic path decides what to do with them
+            sets = []
+            for dt, sel in by_dt:
+                if sel:
+                    moms, first_run = self.get_momentums(sel)
+                    sets.append({'dtype': dt, 'params': sel, 'moms': moms, 'first_run': first_run})
+            return sets
+
+        c = self._fast.get(gid, group, build)
+        done = []
+        if c is None:
+            return done
+        for st in c['sets']:
+            try:
+                self.multi_tensor_sgd(multi_tensor_applier.chunk_size, self._dummy_overflow_buf, [st['params'], st['moms']],
+                                      group['weight_decay'], group['momentum'], group['dampening'], group['lr'],
+                                      group['nesterov'], st['first_run'], self.wd_after_momentum,
+                                      1.0 / self.most_recent_scale, grads_of=0)
+            except RuntimeError as e:
+                if not is_fallback(e):
+                    raise
+                return done
+            st['first_run'] = False
+            done.append(st['dtype'])
+        return done
 
     def zero_grad(self, set_to_none=None):
         if self.set_grad_none if set_to_none is None else set_to_none:
@@ -111,10 +155,12 @@ class FusedSGD(torch.optim.Optimizer):
                 launch_sets = [[grads16, fp32_from_fp16_params, fp32_from_fp16_momentums, fp16_model_params],
                                [fp32_grads, fp32_params, fp32_momentums]]
             else:
-                fp16_params = [p for p in group['params'] if (p.dtype == torch.float16 and p.grad is not None)]
+                done = self._fast_step(gid, group)
+                want = lambda p, dt: p.dtype == dt and dt not in done and p.grad is not None
+                fp16_params = [p for p in group['params'] if want(p, torch.float16)] if torch.float16 not in done else []
                 fp16_grads = [_grad_in_param_layout(p) for p in fp16_params]
                 fp16_momentums, first_runs[0] = self.get_momentums(fp16_params)
-                fp32_params = [p for p in group['params'] if (p.dtype == torch.float32 and p.grad is not None)]
+                fp32_params = [p for p in group['params'] if want(p, torch.float32)] if torch.float32 not in done else []
                 fp32_grads = [_grad_in_param_layout(p) for p in fp32_params]
                 fp32_momentums, first_runs[1] = self.get_momentums(fp32_params)
                 launch_sets = [[fp16_grads, fp16_params, fp16_momentums], [fp32_grads, fp32_params, fp32_momentums]]

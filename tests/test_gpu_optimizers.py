@@ -294,3 +294,78 @@ def test_fused_adam_master_weights_and_capturable():
         assert bits_equal(mx, my) and bits_equal(x, y)           # eager == graph replay
         assert bits_equal(x.detach(), mx.bfloat16())             # model copy is the rounded master
         assert rel_close(mx, r, 2e-6, 2e-7)
+
+
+# ------------------------------------------------------------------------------------------------ steady-state fast path
+def _mk(sizes, dtype=torch.float32, seed=3):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return [torch.nn.Parameter(torch.randn(s, device="cuda", generator=g).to(dtype) * 0.1) for s in sizes]
+
+
+def _set_grads(params, it, skip=()):
+    for i, p in enumerate(params):
+        if i in skip:
+            p.grad = None
+            continue
+        g = torch.Generator(device="cuda").manual_seed(1000 * it + i)
+        p.grad = (torch.randn(p.shape, device="cuda", generator=g) * 1e-2).to(p.dtype)
+
+
+@pytest.mark.parametrize("which", ["sgd", "adam", "lamb"])
+def test_fast_path_is_bit_identical_to_generic_path_and_falls_back(which):
+    """The cached-list / grads_of route must produce the same bits as the generic per-step list building, take over after
+    the first step, and hand a step back to the generic route when a gradient is missing (then resume)."""
+    from beforeholiday_b200.optimizers import FusedAdam, FusedLAMB, FusedSGD
+
+    sizes = [(33, 17), (1000,), (4097,), (64, 3, 3, 3), (1,)]
+    ctor = {"sgd": lambda ps: FusedSGD(ps, lr=0.1, momentum=0.9, dampening=0.1, weight_decay=1e-4),
+            "adam": lambda ps: FusedAdam(ps, lr=1e-3, weight_decay=0.01),
+            "lamb": lambda ps: FusedLAMB(ps, lr=1e-3, weight_decay=0.01, max_grad_norm=0.05)}[which]
+    dts = [torch.float32, torch.float16, torch.float32, torch.float32, torch.float16]
+    pa = [torch.nn.Parameter(p.detach().clone()) for p in (_mk([s], dt)[0] for s, dt in zip(sizes, dts))]
+    pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
+    # channels_last parameter: its gradient arrives contiguous -> layout differs -> that step uses the generic path
+    fast, slow = ctor(pa), ctor(pb)
+    slow._fast.enabled = False
+    amp_C = __import__("beforeholiday_b200").load_amp_C()
+    for it in range(6):
+        skip = (2,) if it == 3 else ()
+        _set_grads(pa, it, skip)
+        _set_grads(pb, it, skip)
+        fast.step()
+        slow.step()
+        for a, b in zip(pa, pb):
+            assert bits_equal(a, b), f"{which}: step {it}"
+    assert fast._fast._cache and not slow._fast._cache
+    for a, b in zip(pa, pb):
+        sa, sb = fast.state[a], slow.state[b]
+        for k in sa:
+            if torch.is_tensor(sa[k]):
+                assert bits_equal(sa[k], sb[k]), k
+    # checkpoint round trip drops the cached lists (the state tensors are replaced)
+    fast.load_state_dict(fast.state_dict())
+    assert not fast._fast._cache
+    _set_grads(pa, 9)
+    _set_grads(pb, 9)
+    fast.step()
+    slow.step()
+    for a, b in zip(pa, pb):
+        assert bits_equal(a, b)
+
+
+def test_grads_of_rejects_what_it_cannot_take(amp_C):
+    p = [torch.nn.Parameter(torch.zeros(8, device="cuda")), torch.nn.Parameter(torch.zeros(8, device="cuda"))]
+    m = [torch.zeros(8, device="cuda") for _ in p]
+    f = torch.zeros(1, dtype=torch.int32, device="cuda")
+    p[0].grad = torch.ones(8, device="cuda")
+    with pytest.raises(RuntimeError, match="grads_of: a parameter has no gradient"):
+        amp_C.multi_tensor_sgd(8192, f, [p, m], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0, grads_of=0)
+    assert float(p[0].detach().abs().sum()) == 0.0   # nothing was launched
+    p[1].grad = torch.ones(16, device="cuda")[::2]
+    with pytest.raises(RuntimeError, match="grads_of: gradient layout differs"):
+        amp_C.multi_tensor_sgd(8192, f, [p, m], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0, grads_of=0)
+    p[1].grad = torch.full((8,), 2.0, device="cuda")
+    amp_C.multi_tensor_sgd(8192, f, [p, m], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0, grads_of=0)
+    assert torch.equal(p[0].detach(), torch.full((8,), -0.1, device="cuda")) and torch.equal(m[1], p[1].grad)
+    n, _ = amp_C.multi_tensor_l2norm(65536, f, [p], False, grads_of=0)
+    assert abs(float(n) - (8 * 1 + 8 * 4) ** 0.5) < 1e-6
