@@ -149,7 +149,8 @@ inline const char* check_entry(PyObject* item, const c10::Device& ref_device, at
     const at::Tensor& x0 = THPVariable_Unpack(item);
     // grad = true: the entry is the .grad of the listed parameter (the optimizers' fast path: no Python-side list of
     // gradients is ever built).  Reading autograd metadata is a pure read; safe on the worker threads.
-    const at::Tensor& x = grad ? x0.grad() : x0;
+    // TensorImpl::grad(), not Tensor::grad(): the latter warns (through Python, needing the GIL) for non-leaf tensors
+    const at::Tensor& x = grad ? x0.unsafeGetTensorImpl()->grad() : x0;
     if (grad) {
         if (!x.defined()) return "grads_of: a parameter has no gradient";
         if (x.is_sparse()) return "grads_of: sparse gradient";
@@ -211,8 +212,9 @@ void flatten(const py::handle& lists_obj, size_t depth_lo, size_t depth_hi, cons
         PyObject* it0 = src[l].items[0];
         TORCH_CHECK(THPVariable_Check(it0), who, ": tensor_lists must contain tensors");
         const at::Tensor& x0 = THPVariable_Unpack(it0);
-        if (src[l].grad) TORCH_CHECK(x0.grad().defined(), "grads_of: a parameter has no gradient");
-        st0[l] = src[l].grad ? x0.grad().scalar_type() : x0.scalar_type();
+        const at::Tensor& g0 = x0.unsafeGetTensorImpl()->grad();
+        if (src[l].grad) TORCH_CHECK(g0.defined(), "grads_of: a parameter has no gradient");
+        st0[l] = src[l].grad ? g0.scalar_type() : x0.scalar_type();
         f.tl.dtype[l] = dtype_tag(st0[l], who);
     }
 

@@ -369,3 +369,14 @@ def test_grads_of_rejects_what_it_cannot_take(amp_C):
     assert torch.equal(p[0].detach(), torch.full((8,), -0.1, device="cuda")) and torch.equal(m[1], p[1].grad)
     n, _ = amp_C.multi_tensor_l2norm(65536, f, [p], False, grads_of=0)
     assert abs(float(n) - (8 * 1 + 8 * 4) ** 0.5) < 1e-6
+
+
+def test_grads_of_on_non_leaf_tensors_does_not_touch_python_warnings(amp_C):
+    """Non-leaf tensors have no .grad and Tensor::grad() would WARN through Python -- from a worker thread that would
+    need the GIL the caller holds.  The extension must read the gradient slot silently, also on the threaded walk."""
+    base = torch.zeros(40000 * 4, device="cuda", requires_grad=True)
+    views = list((base * 1.0).split(4))            # 40 000 non-leaf tensors: the threaded walk (>= 32768 entries)
+    moms = [torch.zeros(4, device="cuda") for _ in views]
+    f = torch.zeros(1, dtype=torch.int32, device="cuda")
+    with pytest.raises(RuntimeError, match="grads_of: a parameter has no gradient"):
+        amp_C.multi_tensor_sgd(8192, f, [views, moms], 0.0, 0.9, 0.0, 0.1, False, True, False, 1.0, grads_of=0)
