@@ -9,7 +9,7 @@ sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import torch  # noqa: E402
 
 import workloads  # noqa: E402
-from beforeholiday_b200.optimizers import FusedAdam, FusedSGD  # noqa: E402
+from beforeholiday_b200.optimizers import FusedAdam, FusedLAMB, FusedSGD  # noqa: E402
 
 
 def make_params(numels):
@@ -50,6 +50,22 @@ def main():
         opt = ctor(ps)
         ms = wall_ms(opt.step)
         print(f"C3 {len(numels)} tensors  {name:36s} step() wall {ms:8.3f} ms", flush=True)
+        del opt, ps
+        torch.cuda.empty_cache()
+    # C4: BERT-large FusedLAMB (398 tensors, 336 M params): generic per-step list building vs the steady-state route
+    numels = workloads.numels(workloads.bert_large())
+    for fast in (False, True):
+        ps = make_params(numels)
+        opt = FusedLAMB(ps, lr=1e-3, weight_decay=0.01, max_grad_norm=1.0)
+        opt._fast.enabled = fast
+
+        def one():
+            # LAMB stage 1 overwrites the gradients with the update term: refill them each iteration (outside the timing
+            # this would be the backward pass); cheap device-side copy
+            opt.step()
+        ms = wall_ms(one)
+        print(f"C4 {len(numels)} tensors  FusedLAMB ({'steady-state route' if fast else 'generic route'})".ljust(56)
+              + f" step() wall {ms:8.3f} ms", flush=True)
         del opt, ps
         torch.cuda.empty_cache()
 
