@@ -58,6 +58,50 @@ def _free_port():
     s.close()
     return p
 
+def _logged(target, rank, *args):
+    """Worker wrapper: a failing rank leaves its traceback in <outdir>/rank<r>.err for the parent to show."""
+    import traceback
+
+    outdir = args[2]
+    try:
+        target(rank, *args)
+    except BaseException:
+        with open(os.path.join(outdir, f"rank{rank}.err"), "w") as f:
+            traceback.print_exc(file=f)
+        raise
+
+
+def _run_workers(target, world, tmp_path, *extra, attempts=2):
+    """Spawn `world` ranks of `target(rank, world, port, outdir, *extra)`.  A failed attempt is retried once on a fresh
+    port (process-group bring-up right after another job's NVLS / symmetric-memory teardown can fail transiently); the
+    assertion message carries the ranks' tracebacks."""
+    import time
+
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    report = ""
+    for attempt in range(attempts):
+        for f in tmp_path.glob("rank*.err"):
+            f.unlink()
+        port = _free_port()
+        procs = [ctx.Process(target=_logged, args=(target, r, world, port, str(tmp_path)) + tuple(extra)) for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(500)
+        codes = [p.exitcode for p in procs]
+        for p in procs:
+            if p.exitcode is None:
+                p.kill()
+        if all(c == 0 for c in codes):
+            return
+        report += f"\nattempt {attempt}: exit codes {codes}\n" + "".join(
+            f"--- {f.name} ---\n{f.read_text()[-3000:]}" for f in sorted(tmp_path.glob("rank*.err")))
+        time.sleep(5)
+    raise AssertionError("distributed workers failed" + report)
+
+
 
 @pytest.mark.timeout(600)
 @pytest.mark.parametrize("fused", [False, "p2p", "mc"], ids=["nccl", "fused_p2p", "fused_multicast"])
@@ -65,16 +109,7 @@ def _free_port():
 def test_sharded_adam_two_gpus_matches_oracle(tmp_path, oracle, fused, world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    import torch.multiprocessing as mp
-
-    ctx = mp.get_context("spawn")
-    port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), fused)) for r in range(world)]
-    for p in procs:
-        p.start()
-    for p in procs:
-        p.join(500)
-        assert p.exitcode == 0
+    _run_workers(_worker, world, tmp_path, fused)
     res = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
     if "skip" in res[0]:
         pytest.skip(res[0]["skip"])
@@ -160,17 +195,8 @@ def _module_worker(rank, world, port, outdir, clip):
 def test_dist_adam_module_vs_ddp_adamw(tmp_path, clip):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    import torch.multiprocessing as mp
-
     world = 2
-    ctx = mp.get_context("spawn")
-    port = _free_port()
-    procs = [ctx.Process(target=_module_worker, args=(r, world, port, str(tmp_path), clip)) for r in range(world)]
-    for p in procs:
-        p.start()
-    for p in procs:
-        p.join(500)
-        assert p.exitcode == 0
+    _run_workers(_module_worker, world, tmp_path, clip)
     res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
     for a, b in zip(res[0]["mine"], res[1]["mine"]):
         assert torch.equal(a, b)                       # every rank holds the same gathered parameters
@@ -227,16 +253,7 @@ def _bucket_worker(rank, world, port, outdir):
 def test_flat_bucket_allreduce_two_gpus(tmp_path):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    import torch.multiprocessing as mp
-
-    ctx = mp.get_context("spawn")
-    port = _free_port()
-    procs = [ctx.Process(target=_bucket_worker, args=(r, 2, port, str(tmp_path))) for r in range(2)]
-    for p in procs:
-        p.start()
-    for p in procs:
-        p.join(500)
-        assert p.exitcode == 0
+    _run_workers(_bucket_worker, 2, tmp_path)
     for r in range(2):
         res = torch.load(tmp_path / f"rank{r}.pt")
         assert all(v is True or v == 1 for v in res.values()), res
@@ -294,20 +311,11 @@ def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world):
         pytest.skip(f"needs {world} GPUs")
     import sys
 
-    import torch.multiprocessing as mp
-
     sys.path.insert(0, os.path.dirname(__file__))
     from lamb_replay import replay
     from oracle import mt_oracle as O
 
-    ctx = mp.get_context("spawn")
-    port = _free_port()
-    procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
-    for p in procs:
-        p.start()
-    for p in procs:
-        p.join(500)
-        assert p.exitcode == 0
+    _run_workers(_lamb_worker, world, tmp_path)
     res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
     for r in range(1, world):
         for a, b in zip(res[0]["params"], res[r]["params"]):
