@@ -24,9 +24,11 @@
 #include <vector>
 
 #include "../../include/mt_b200.h"
+#include "walk_pool.h"
 
 namespace {
 
+using mt_host::WalkPool;
 using TensorLists = py::object;  // list[list[Tensor]], walked in place (see flatten())
 
 int dtype_tag(at::ScalarType t, const char* who) {
@@ -61,75 +63,6 @@ struct FastSeq {
     PyObject* operator[](Py_ssize_t i) const { return PySequence_Fast_GET_ITEM(o, i); }
     FastSeq(const FastSeq&) = delete;
     FastSeq& operator=(const FastSeq&) = delete;
-};
-
-// A few persistent worker threads for walking long lists (creating and joining 8 std::threads per call costs about as
-// much as the walk itself at 50k tensors).  Workers only read tensor metadata; they never call into Python.  The pool
-// is leaked on purpose (no static destructor racing interpreter shutdown) and rebuilt in a forked child.
-class WalkPool {
-  public:
-    static WalkPool& get() {
-        static WalkPool* pool = nullptr;
-        static pid_t owner = 0;
-        static std::mutex mu;
-        std::lock_guard<std::mutex> lk(mu);
-        if (!pool || owner != getpid()) {
-            pool = new WalkPool(std::min(7u, std::max(1u, std::thread::hardware_concurrency() / 2) - 1));
-            owner = getpid();
-        }
-        return *pool;
-    }
-    unsigned workers() const { return (unsigned)threads_.size(); }
-    // run fn(part) for part in [0, parts): part 0 on the caller, the rest on the workers; parts <= workers() + 1
-    void run(unsigned parts, const std::function<void(unsigned)>& fn) {
-        std::lock_guard<std::mutex> serial(run_mu_);   // one parallel walk at a time (callers hold the GIL anyway)
-        {
-            std::lock_guard<std::mutex> lk(mu_);
-            fn_ = &fn;
-            parts_ = parts;
-            next_ = 1;
-            pending_ = parts - 1;
-            generation_++;
-        }
-        cv_.notify_all();
-        fn(0);
-        std::unique_lock<std::mutex> lk(mu_);
-        done_.wait(lk, [&] { return pending_ == 0; });
-        fn_ = nullptr;
-    }
-
-  private:
-    explicit WalkPool(unsigned n) {
-        for (unsigned i = 0; i < n; i++) {
-            threads_.emplace_back([this] { loop(); });
-            threads_.back().detach();
-        }
-    }
-    void loop() {
-        uint64_t seen = 0;
-        for (;;) {
-            unsigned part;
-            const std::function<void(unsigned)>* fn;
-            {
-                std::unique_lock<std::mutex> lk(mu_);
-                cv_.wait(lk, [&] { return generation_ != seen && next_ < parts_; });
-                part = next_++;
-                if (next_ >= parts_) seen = generation_;
-                fn = fn_;
-            }
-            (*fn)(part);
-            {
-                std::lock_guard<std::mutex> lk(mu_);
-                if (--pending_ == 0) done_.notify_one();
-            }
-        }
-    }
-    std::vector<std::thread> threads_;
-    std::mutex mu_, run_mu_;
-    std::condition_variable cv_, done_;
-    const std::function<void(unsigned)>* fn_ = nullptr;
-    unsigned parts_ = 0, next_ = 0, pending_ = 0;
-    uint64_t generation_ = 0;
 };
 
 // torch.nn.Parameter instances are THPVariable objects of a subclass type: same layout, no __torch_function__ games.
