@@ -2,8 +2,9 @@
 """Build the REFERENCE's own multi-tensor extensions, unmodified, into oracle/_ref/.
 
 TEST INFRASTRUCTURE ONLY.  Nothing under beforeholiday_b200/ imports this or the
-libraries it produces; only tests/, __graft_entry__.smoke() and bench.py's
-reference legs may load oracle/_ref/*.so, and only as the checker / baseline.
+libraries it produces; only tests/, __graft_entry__.smoke(), bench.py's
+reference legs and the measurement scripts under tools/ (bench_ops.py: the same baseline legs for the other configs)
+may load oracle/_ref/*.so, and only as the checker / baseline.
 
 What is built (sources are compiled where they lie under /root/reference; none
 are copied into this repository):

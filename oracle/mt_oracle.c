@@ -3,8 +3,9 @@
  *
  * TEST INFRASTRUCTURE ONLY.  This file is the parity checker for the CUDA
  * product in beforeholiday_b200/csrc; it is never linked into, imported by or
- * executed from the product path.  Only tests/, __graft_entry__.smoke() and
- * bench.py's cpu_baseline / --impl reference legs may load it.
+ * executed from the product path.  Only tests/, __graft_entry__.smoke(),
+ * bench.py's cpu_baseline / --impl reference legs and tools/bench_ops.py (the same
+ * baseline leg for the other configs) may load it.
  *
  * Arithmetic contract: every functor is restated in IEEE-754 binary32 with the
  * SAME operation order as the reference's device code and NO fused

@@ -1,7 +1,8 @@
 """ctypes front-end of the CPU oracle (oracle/mt_oracle.c) on torch CPU tensors.
 
 TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
-cpu_baseline / --impl reference legs.  Nothing under beforeholiday_b200/ imports it.
+cpu_baseline / --impl reference legs (and tools/bench_ops.py, which extends those baseline legs to the other configs:
+the CPU step timed beside a GPU number).  Nothing under beforeholiday_b200/ imports it.
 
 The functions mirror the reference's ``amp_C`` operator signatures
 (csrc/amp_C_frontend.cpp:165-194 in /root/reference) but run on CPU tensors, so a parity

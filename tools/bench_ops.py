@@ -5,6 +5,10 @@
     python tools/bench_ops.py [--configs c1,c2,c3,c4] [--iters 10]
 
 Prints one JSON object per measurement to stdout.
+
+Measurement infrastructure, not product: like bench.py's `reference_cuda` / `cpu_baseline` legs it loads oracle/_ref (the
+reference's kernels) and oracle/mt_oracle (the CPU restatement) as BASELINES timed beside this library; nothing under
+beforeholiday_b200/ imports either.
 """
 from __future__ import annotations
 
