@@ -267,3 +267,64 @@ def test_sharded_lamb_world2_matches_single_process(tmp_path):
         ia, ib = a.view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
         assert int((ia - ib).abs().max()) <= 1          # bf16 copies within 1 ulp (norm summation order)
         assert float((ia != ib).float().mean()) < 0.01
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The drop-in use with a real module (the scenario of tests/test_gpu_dist.py::test_dist_adam_module_vs_ddp_adamw, modelled
+# on the reference's apex/contrib/test/optimizers/test_dist_adam.py:84-156) on CPU: param groups with different weight
+# decay, parameters and gradients re-pointed at views of the flat buffers, tiny buckets so that fragments straddle
+# sub-shards -- against torch.optim.AdamW on the rank-averaged gradients.
+def _module_cpu_worker(rank, world, port, outdir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        mk = lambda: torch.nn.Sequential(*[torch.nn.Linear(7, 7) for _ in range(11)])
+        model, ref = mk(), mk()
+        ref.load_state_dict(model.state_dict())
+        decay = [p for n, p in model.named_parameters() if n.endswith("weight")]
+        no_decay = [p for n, p in model.named_parameters() if n.endswith("bias")]
+        opt = CpuShardedAdam([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
+                             lr=1e-2, betas=(0.9, 0.95), eps=1e-8, bucket_cap_mb=71 * 4 / 2 ** 20)
+        assert opt.layout.nbuckets > 1 and opt.grads_flat.dtype == torch.float32
+        assert all(p.data_ptr() == opt.params_flat.data_ptr() + 4 * o for p, o in zip(decay + no_decay, opt.layout.offsets))
+        rdecay = [p for n, p in ref.named_parameters() if n.endswith("weight")]
+        rno = [p for n, p in ref.named_parameters() if n.endswith("bias")]
+        ropt = torch.optim.AdamW([{"params": rdecay, "weight_decay": 0.1}, {"params": rno, "weight_decay": 0.0}],
+                                 lr=1e-2, betas=(0.9, 0.95), eps=1e-8)
+        for it in range(4):
+            opt.zero_grad()
+            ropt.zero_grad()
+            g = torch.Generator().manual_seed(1000 * it + rank)
+            x = torch.randn(16, 7, generator=g)
+            model(x).pow(2).mean().backward()          # accumulates straight into the flat gradient buffer's views
+            assert all(p.grad.data_ptr() == opt.grads_flat.data_ptr() + 4 * o
+                       for p, o in zip(decay + no_decay, opt.layout.offsets))
+            ref(x).pow(2).mean().backward()
+            for p in ref.parameters():
+                dist.all_reduce(p.grad)
+                p.grad /= world
+            opt.step()
+            ropt.step()
+        torch.save({"mine": [p.detach().clone() for p in model.parameters()],
+                    "ref": [p.detach().clone() for p in ref.parameters()]}, os.path.join(outdir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_sharded_adam_on_a_real_module_world2_vs_adamw(tmp_path):
+    world = 2
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_module_cpu_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
+    for a, b in zip(res[0]["mine"], res[1]["mine"]):
+        assert torch.equal(a, b)
+    for a, b in zip(res[0]["mine"], res[0]["ref"]):
+        assert torch.allclose(a, b, rtol=2e-5, atol=2e-6)
