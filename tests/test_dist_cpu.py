@@ -236,14 +236,14 @@ def _lamb_worker(rank, world, port, outdir):
 
 
 @pytest.mark.timeout(300)
-def test_sharded_lamb_world2_matches_single_process(tmp_path):
+@pytest.mark.parametrize("world", [2, 4])
+def test_sharded_lamb_matches_single_process(tmp_path, world):
     import sys
 
     sys.path.insert(0, os.path.dirname(__file__))
     from lamb_replay import replay
     from oracle import mt_oracle as O
 
-    world = 2
     ctx = mp.get_context("spawn")
     port = _free_port()
     procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
@@ -253,8 +253,9 @@ def test_sharded_lamb_world2_matches_single_process(tmp_path):
         p.join(240)
         assert p.exitcode == 0
     res = {r: torch.load(tmp_path / f"rank{r}.pt") for r in range(world)}
-    for a, b in zip(res[0], res[1]):
-        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    for r in range(1, world):
+        for a, b in zip(res[0], res[r]):
+            assert torch.equal(a.view(torch.int16), b.view(torch.int16))
     torch.manual_seed(0)
     init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
     order = init[0::2] + init[1::2]
