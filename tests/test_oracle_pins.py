@@ -274,3 +274,102 @@ def test_dist_lamb_combined_scale(oracle):
     want_m = (1 - torch.tensor(0.9)) * (g / torch.tensor(cs, dtype=torch.float32))
     assert rel_close(m, want_m, 1e-6, 1e-9)
     assert abs(float((g / cs).double().norm()) - 1.0) < 1e-4      # the clipped, unscaled gradient has norm max_norm
+
+
+# ---------------------------------------------------------------------------------------- 5. the "next" optimizers
+GOLD_NOVO = torch.load(Path(__file__).parent / "golden" / "ref_novograd.pt", weights_only=False)
+
+
+@pytest.mark.parametrize("case", sorted(GOLD_NOVO["cases"]))
+def test_novograd_vs_reference_python_golden(oracle, case):
+    """multi_tensor_novograd restatement (csrc/multi_tensor_novograd.cu:66-121 + the norm blend of
+    multi_tensor_l2norm_kernel.cu:272-298) against the pure-torch Novograd the reference's own test compares
+    FusedNovoGrad with (tests/L0/run_optimizers/test_fused_novograd.py:10-114; fixture made by
+    tests/golden/make_golden_novograd.py), driven the way apex/optimizers/fused_novograd.py:118-214 drives the kernel:
+    norms initialised with the first step's gradient norm, no bias correction, regularisation inside the moment, L2
+    norm.  Tolerances: the reference test's 1e-3 absolute / relative (:test_fused_optimizer.py:13-16) and 2e-5."""
+    gold = GOLD_NOVO["cases"][case]
+    opts, sizes = gold["opts"], GOLD_NOVO["SIZES"]
+    g0 = torch.Generator()
+    ps = [(torch.randn(n, generator=g0.manual_seed(300 + i)) * 0.1) for i, n in enumerate(sizes)]
+    ms = [torch.zeros(n) for n in sizes]
+    norms = None
+    for it in range(GOLD_NOVO["ITERS"]):
+        gs = [(torch.randn(n, generator=g0.manual_seed(4000 + 10 * it + i)) * 0.05) for i, n in enumerate(sizes)]
+        if norms is None:   # init_zero=False: "init with first step norm, so first blend have no effect" (:167-176)
+            norms = torch.tensor([float(torch.sum(torch.pow(g, 2)).sqrt()) for g in gs])
+        oracle.multi_tensor_novograd(8192, flag(), [gs, ps, ms], norms, opts["lr"], opts["betas"][0], opts["betas"][1],
+                                     opts["eps"], it + 1, 0, opts["weight_decay"], 1 if opts["grad_averaging"] else 0, 0, 2)
+    for p, gp in zip(ps, gold["params"]):
+        assert (p - gp).abs().max() <= 1e-3
+        assert rel_close(p, gp, 2e-5, 1e-7)
+    for m, gm in zip(ms, gold["exp_avg"]):
+        assert rel_close(m, gm, 2e-5, 1e-7)
+    # the fused op keeps the NORM, the python reference its square
+    for n, gv in zip(norms, gold["exp_avg_sq"]):
+        assert abs(float(n) ** 2 - float(gv)) <= 2e-5 * float(gv)
+
+
+@pytest.mark.parametrize("wd", [0.0, 1e-3])
+def test_adagrad_vs_torch_optim(oracle, wd):
+    """AdagradFunctor restatement, mode 0 (L2), against torch.optim.Adagrad -- the oracle of the reference's
+    TestFusedAdagrad (tests/L0/run_optimizers/test_fused_optimizer.py:92-139: lr 5e-4, eps 1e-8, weight_decay 1e-3)."""
+    torch.manual_seed(9876)
+    p = torch.rand(N)
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adagrad([ref], lr=5e-4, eps=1e-8, weight_decay=wd)
+    h = torch.zeros(N)
+    for it in range(ITERS):
+        g = gen_inputs(6000 + it, N).abs() % 1.0
+        ref.grad = g.clone()
+        opt.step()
+        oracle.multi_tensor_adagrad(8192, flag(), [[g], [p], [h]], 5e-4, 1e-8, 0, wd)
+    assert (p - ref.data).abs().max() <= 1e-3
+    assert rel_close(p, ref.data, 1e-6, 2e-7)
+    assert rel_close(h, opt.state[ref]["sum"], 1e-6, 1e-9)
+
+
+@pytest.mark.parametrize("mode,wd,nv", [(1, 0.01, False), (0, 0.01, True), (1, 0.0, False)])
+def test_lamb_mp_reproduces_pinned_lamb(oracle, mode, wd, nv):
+    """The "_mp" LAMB restatement (csrc/multi_tensor_lamb_mp.cu) with inv_scale = 1 and fp32 everywhere is the same
+    arithmetic as multi_tensor_lamb, which is pinned against the reference's RefLAMB above: bit for bit, incl. norms."""
+    sizes = [5001, 33, 70001]
+    ps = [gen_inputs(100 + i, k).abs() * 0.5 + 0.01 for i, k in enumerate(sizes)]
+    ms, vs = [torch.zeros(k) for k in sizes], [torch.zeros(k) for k in sizes]
+    ps2, ms2, vs2 = [x.clone() for x in ps], [x.clone() for x in ms], [x.clone() for x in vs]
+    for it in range(3):
+        gs = [gen_inputs(1000 + 10 * it + i, k) * 0.1 for i, k in enumerate(sizes)]
+        gs2 = [g.clone() for g in gs]
+        gnorm, _ = oracle.multi_tensor_l2norm(65536, flag(), [gs], False)
+        oracle.multi_tensor_lamb(8192, flag(), [gs, ps, ms, vs], 5e-4, 0.9, 0.999, 1e-6, it + 1, 1, wd, 1, mode, gnorm, 1.0, nv)
+        oracle.multi_tensor_lamb_mp(8192, flag(), [gs2, ps2, ms2, vs2], torch.tensor(5e-4), 0.9, 0.999, 1e-6,
+                                    torch.tensor([it + 1], dtype=torch.int32), 1, wd, 1, mode, gnorm, torch.tensor([1.0]), nv,
+                                    torch.zeros(1), torch.tensor([1.0]))
+        for a, b in zip(gs + ps + ms + vs, gs2 + ps2 + ms2 + vs2):
+            assert bits_equal(a, b)
+
+
+@pytest.mark.parametrize("nesterov", [False, True])
+def test_lars_without_trust_ratio_is_torch_sgd_and_ratio_formula(oracle, nesterov):
+    """LARSFunctor restatement (csrc/multi_tensor_lars.cu:84-135).  With the layer-wise ratio switched off (is_skipped, the
+    reference's route for biases / norm layers) it is SGD with momentum in the "velocity carries -lr" form, i.e.
+    torch.optim.SGD at constant lr; with it, the step is scaled by tc*|w| / (|g| + wd*|w| + eps) (:96-104)."""
+    torch.manual_seed(9876)
+    w = torch.rand(N)
+    ref = torch.nn.Parameter(w.clone())
+    opt = torch.optim.SGD([ref], lr=0.05, momentum=0.9, weight_decay=1e-4, nesterov=nesterov)
+    mom = torch.zeros(N)
+    for it in range(ITERS):
+        g = gen_inputs(7000 + it, N) * 0.1
+        ref.grad = g.clone()
+        opt.step()
+        oracle.multi_tensor_lars(8192, flag(), [[g], [w], [mom]], [1.0], [1.0], 0.05, 0.001, 0.0, 1e-4, 0.9, 0.0, nesterov,
+                                 False, False, 1.0, True)
+    assert rel_close(w, ref.data, 1e-6, 2e-7)
+    # one step WITH the ratio, from zero momentum: w' = w - lr*trust*(g + wd*w)
+    w2, g2, m2 = torch.rand(N), gen_inputs(7100, N) * 0.1, torch.zeros(N)
+    gn, pn = float(g2.double().norm()), float(w2.double().norm())
+    want = w2 - 0.05 * (0.001 * pn / (gn + pn * 1e-4 + 1e-8)) * (g2 + 1e-4 * w2) * (1.9 if nesterov else 1.0)
+    oracle.multi_tensor_lars(8192, flag(), [[g2], [w2], [m2]], [gn], [pn], 0.05, 0.001, 1e-8, 1e-4, 0.9, 0.0, nesterov, False,
+                             False, 1.0, False)
+    assert rel_close(w2, want, 2e-6, 1e-8)
