@@ -104,3 +104,20 @@ def test_product_does_not_import_the_oracle():
             assert not py.search(p.read_text()), p
         elif p.suffix in (".cu", ".cuh", ".cpp", ".h"):
             assert not cc.search(p.read_text()), p
+
+
+def test_applier_forwards_with_its_chunk_size_and_reports_availability():
+    from beforeholiday_b200.multi_tensor_apply import MultiTensorApply, multi_tensor_applier, multi_tensor_applier_l2norm
+
+    assert MultiTensorApply.available and multi_tensor_applier.available and MultiTensorApply.import_err is None
+    assert (multi_tensor_applier.chunk_size, multi_tensor_applier_l2norm.chunk_size) == (256 * 32, 2048 * 32)
+    seen = []
+    out = multi_tensor_applier(lambda *a: seen.append(a) or "ret", "flag", [["t"]], 1.5, True)
+    assert out == "ret" and seen == [(8192, "flag", [["t"]], 1.5, True)]
+    # unavailable extension: every call raises with the original import error in the message
+    MultiTensorApply.available, MultiTensorApply.import_err = False, ImportError("no such file")
+    try:
+        with pytest.raises(RuntimeError, match="did not import.*no such file"):
+            multi_tensor_applier(lambda *a: None, None, [[]])
+    finally:
+        MultiTensorApply.available, MultiTensorApply.import_err = True, None
