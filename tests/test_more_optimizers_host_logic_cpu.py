@@ -81,3 +81,67 @@ def test_fused_lars_driver_applies_the_layerwise_ratio(oracle, is_skipped):
         want = w - lr * ratio * (g + wd * w)                   # first step from zero momentum
         assert torch.allclose(p.detach(), want, rtol=2e-6, atol=1e-8)
         assert torch.allclose(opt.state[p]["momentum_buffer"], -(lr * ratio) * (g + wd * w), rtol=2e-6, atol=1e-9)
+
+
+def test_fused_mixed_precision_lamb_driver_matches_lamb_and_keeps_masters(oracle):
+    """FusedMixedPrecisionLamb's driver (device-side lr / step tensors, fp32 masters for reduced-precision parameters,
+    model copy written by the kernel) over the "_mp" restatements == the RefLAMB-pinned multi_tensor_lamb on fp32 copies
+    of the same parameters; the 16-bit model parameters are the rounded masters."""
+    from beforeholiday_b200.optimizers import FusedMixedPrecisionLamb
+
+    gen = torch.Generator()
+    sizes = [4099, 33, 257]
+    init = [(torch.randn(n, generator=gen.manual_seed(50 + i)) * 0.1).half() for i, n in enumerate(sizes)]
+    params = [torch.nn.Parameter(x.clone()) for x in init]
+    opt = FusedMixedPrecisionLamb(params, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01, max_grad_norm=1.0,
+                                  reduced_precision_dtype=torch.float16)
+    opt.multi_tensor_l2norm = lambda chunk, flag, lists, per: oracle.multi_tensor_l2norm_mp(chunk, flag, _detached(lists), per)
+    opt.multi_tensor_lamb = lambda chunk, flag, lists, *a: oracle.multi_tensor_lamb_mp(chunk, flag, _detached(lists), *a)
+    p32 = [x.float() for x in init]
+    m, v = [torch.zeros(n) for n in sizes], [torch.zeros(n) for n in sizes]
+    for it in range(4):
+        grads = [(torch.randn(n, generator=gen.manual_seed(900 + 10 * it + i)) * 0.05).half() for i, n in enumerate(sizes)]
+        for p, g in zip(params, grads):
+            p.grad = g.clone()
+        opt.step()
+        # replay: the kernel sees fp16 gradients, fp32 masters; the update term is stored in the gradient dtype (fp16)
+        gs = [g.clone() for g in grads]
+        f = torch.zeros(1, dtype=torch.int32)
+        gn, _ = oracle.multi_tensor_l2norm(65536, f, [gs], False)
+        copies = [torch.zeros(n, dtype=torch.float16) for n in sizes]
+        oracle.multi_tensor_lamb_mp(8192, f, [gs, p32, m, v, copies], torch.tensor(2e-3), 0.9, 0.999, 1e-6,
+                                    torch.tensor([it + 1], dtype=torch.int32), 1, 0.01, 1, 1, gn, torch.tensor([1.0]), False,
+                                    torch.zeros(1), torch.ones(1))
+        for p, c in zip(params, copies):
+            assert torch.equal(p.detach().view(torch.int16), c.view(torch.int16)), f"step {it}"
+    assert int(opt.param_groups[0]['step']) == 4
+    for full, want, p in zip(opt.param_groups_full_precision[0]['params'], p32, params):
+        assert torch.equal(full, want)                                         # fp32 masters carried by the optimizer
+        assert torch.equal(p.detach(), full.half())
+    # a raised found-inf flag: nothing moves and the step counter stays
+    class Scaler:
+        def _check_inf_per_device(self, o):
+            return {params[0].device: torch.ones(1)}
+
+        def _get_scale_async(self):
+            return torch.tensor([1024.0])
+    before = [p.detach().clone() for p in params]
+    for p in params:
+        p.grad = torch.ones_like(p)
+    opt.step(grad_scaler=Scaler())
+    assert all(torch.equal(a, b.detach()) for a, b in zip(before, params)) and int(opt.param_groups[0]['step']) == 4
+
+
+def test_clip_grad_norm_defers_to_torch_off_gpu():
+    from beforeholiday_b200.contrib.clip_grad import clip_grad_norm_
+
+    torch.manual_seed(0)
+    a = [torch.nn.Parameter(torch.randn(50)), torch.nn.Parameter(torch.randn(3, 7))]
+    b = [torch.nn.Parameter(p.detach().clone()) for p in a]
+    for p, q in zip(a, b):
+        p.grad = torch.randn_like(p) * 3
+        q.grad = p.grad.clone()
+    n1 = clip_grad_norm_(a, 1.0)
+    n2 = torch.nn.utils.clip_grad_norm_(b, 1.0)
+    assert torch.equal(n1, n2) and all(torch.equal(p.grad, q.grad) for p, q in zip(a, b))
+    assert float(clip_grad_norm_([torch.nn.Parameter(torch.zeros(3))], 1.0)) == 0.0   # no gradients at all
