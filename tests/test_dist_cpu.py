@@ -63,9 +63,14 @@ class CpuShardedAdam(DistributedFusedAdam):
         from oracle import mt_oracle as O
 
         lists, hp = self._per_bucket[b]
-        if lists[0]:
-            O.multi_tensor_fused_adam(8192, self.noop, lists, *[h.tolist() for h in hp], self.lr, grad_scale,
+        if lists[0]:   # grad_scale is a 1-element tensor on the clipped route (device-side divisor in the product)
+            O.multi_tensor_fused_adam(8192, self.noop, lists, *[h.tolist() for h in hp], self.lr, float(grad_scale),
                                       self.step_count, 1 if self.adam_w_mode else 0, honour_noop=True)
+
+    def grad_norm(self, grads_are_reduced=True):
+        sq = sum((l.double() ** 2).sum() for (lists, _) in self._per_bucket for l in lists[3]).float().reshape(1)
+        dist.all_reduce(sq, group=self.group)
+        return sq.sqrt()
 
 
 def _worker(rank, world, port, outdir):
@@ -275,7 +280,7 @@ def test_sharded_lamb_matches_single_process(tmp_path, world):
 # on the reference's apex/contrib/test/optimizers/test_dist_adam.py:84-156) on CPU: param groups with different weight
 # decay, parameters and gradients re-pointed at views of the flat buffers, tiny buckets so that fragments straddle
 # sub-shards -- against torch.optim.AdamW on the rank-averaged gradients.
-def _module_cpu_worker(rank, world, port, outdir):
+def _module_cpu_worker(rank, world, port, outdir, clip=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -305,7 +310,12 @@ def _module_cpu_worker(rank, world, port, outdir):
             for p in ref.parameters():
                 dist.all_reduce(p.grad)
                 p.grad /= world
-            opt.step()
+            if clip:
+                rn = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.05)
+                n = opt.step(max_grad_norm=0.05)
+                assert abs(float(n) - float(rn)) <= 1e-5 * float(rn) and float(rn) > 0.05   # it really clips
+            else:
+                opt.step()
             ropt.step()
         torch.save({"mine": [p.detach().clone() for p in model.parameters()],
                     "ref": [p.detach().clone() for p in ref.parameters()]}, os.path.join(outdir, f"rank{rank}.pt"))
@@ -314,11 +324,12 @@ def _module_cpu_worker(rank, world, port, outdir):
 
 
 @pytest.mark.timeout(300)
-def test_sharded_adam_on_a_real_module_world2_vs_adamw(tmp_path):
+@pytest.mark.parametrize("clip", [False, True], ids=["plain", "clip_grad_norm"])
+def test_sharded_adam_on_a_real_module_world2_vs_adamw(tmp_path, clip):
     world = 2
     ctx = mp.get_context("spawn")
     port = _free_port()
-    procs = [ctx.Process(target=_module_cpu_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    procs = [ctx.Process(target=_module_cpu_worker, args=(r, world, port, str(tmp_path), clip)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
