@@ -54,6 +54,13 @@ def test_scratch_size_queries():
     tl.numel = C.cast(numel, C.POINTER(C.c_int64))
     assert L.mt_norm_scratch_bytes(65536, C.byref(tl)) == 4 * (3 + 0 + 1)
     assert L.mt_norm_scratch_bytes(1 << 30, C.byref(tl)) == 4 * 2
+    # element-wise families pick their own tile: 16384 elements once that yields >= 4 waves of 4 CTAs/SM (148 SMs assumed
+    # without a device), shrinking to 8192 / 4096 / 2048 for smaller problems.  Sharded LAMB scratch = 2 floats per tile.
+    L.mt_dist_lamb_scratch_bytes.restype = C.c_size_t
+    for n0, tile in ((2048 * 3 + 1, 2048), (16384 * 3000, 16384), (8192 * 2400 + 5, 8192), (4096 * 2368, 4096)):
+        numel[0], numel[1], numel[2] = n0, 0, 10
+        tiles = -(-n0 // tile) + 0 + 1
+        assert L.mt_dist_lamb_scratch_bytes(C.byref(tl)) == 2 * 4 * tiles, (n0, tile)
 
 
 def test_amp_C_exports_reference_names():
