@@ -36,7 +36,8 @@ class MtTensorLists(C.Structure):
 
 
 class MtCacheStats(C.Structure):
-    _fields_ = [(n, C.c_uint64) for n in ("hits", "misses", "uploads_bytes", "entries", "device_bytes")]
+    _fields_ = [(n, C.c_uint64) for n in ("hits", "misses", "uploads_bytes", "entries", "device_bytes",
+                                           "evictions", "cross_stream_waits")]
 
 
 _lib = None

@@ -596,6 +596,8 @@ py::dict table_cache_stats(int device) {
     d["uploads_bytes"] = s.uploads_bytes;
     d["entries"] = s.entries;
     d["device_bytes"] = s.device_bytes;
+    d["evictions"] = s.evictions;
+    d["cross_stream_waits"] = s.cross_stream_waits;
     return d;
 }
 

@@ -76,7 +76,7 @@ extern "C" int mt_multi_tensor_lamb_compute_update_term(
     const int need_norms = seg_sq_out ? 1 : 0;
     if (need_norms && (!seg_begin || nseg <= 0))
         return set_error(MT_EINVAL, "multi_tensor_lamb_compute_update_term: seg_sq_out needs seg_begin and nseg > 0");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     float* partials = static_cast<float*>(scratch);
@@ -131,7 +131,7 @@ extern "C" int mt_multi_tensor_lamb_update_weights(int chunk_size, int32_t* noop
                                     "per_tensor_decay must be device pointers");
     if (tl->dtype[0] != MT_F32 || tl->dtype[1] != MT_F32)
         return set_error(MT_EINVAL, "multi_tensor_lamb_update_weights: the update term and p must be float32");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[2], Tc, "multi_tensor_lamb_update_weights", {

@@ -61,7 +61,7 @@ extern "C" int mt_multi_tensor_adagrad(int chunk_size, int32_t* noop_flag, const
     MT_PROLOGUE("multi_tensor_adagrad", 3, 3)
     if (tl->dtype[1] != tl->dtype[0] || tl->dtype[2] != tl->dtype[0])
         return set_error(MT_EINVAL, "multi_tensor_adagrad: g, p, h must share one dtype (as the reference assumes)");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHBD(tl->dtype[0], Tp, "multi_tensor_adagrad", {
@@ -94,7 +94,7 @@ extern "C" int mt_multi_tensor_novograd(int chunk_size, int32_t* noop_flag, cons
     //    gradient list (tile == chunk, so the flag has the reference's granularity), then the per-tensor blend.
     MtTensorLists gl = *tl;
     gl.depth = 1;
-    DevTable tn;
+    TableRef tn;
     rc = get_table(&gl, chunk_size, stream, &tn);
     if (rc) return rc;
     const size_t need = (size_t)tn.ntiles * sizeof(float);
@@ -127,7 +127,7 @@ extern "C" int mt_multi_tensor_novograd(int chunk_size, int32_t* noop_flag, cons
         MT_CUDA_OK(cudaGetLastError());
     }
     // 2. the update
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHBD(tl->dtype[0], Tp, "multi_tensor_novograd", {
@@ -150,7 +150,7 @@ extern "C" int mt_multi_tensor_lars(int chunk_size, int32_t* noop_flag, const Mt
     if (tl->dtype[2] != wt) return set_error(MT_EINVAL, "multi_tensor_lars: momentum dtype must equal the weight dtype");
     if (tl->depth == 4 && tl->dtype[3] != MT_F16)
         return set_error(MT_EINVAL, "Additional output tensors should always be fp16.");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
 #define MT_LARS(TG, TW, COPY)                                                                                 \

@@ -15,14 +15,19 @@
 // Rules that follow from sharing one array:
 //   * Sizes are capped (MT_NOALLOC_MAX_TENSORS tensors, MT_NOALLOC_MAX_CHUNKS chunks in total); larger requests are
 //     refused with MT_EINVAL and a message, nothing is launched.
-//   * The array keeps whatever the previous call left in it.  Nothing in it has to start at zero: each call first
-//     overwrites the table region, and the finalize pass reads exactly the partials [0, nchunks) that the same call's
-//     first pass has just written (one per chunk, assigned -- never accumulated).  So no clearing is done, and a
-//     shorter call after a longer one cannot see stale partials.
+//   * The array keeps whatever the previous call left in it.  Each call first overwrites the table region, and the
+//     reduction reads exactly the partials [0, nchunks) that the same call has just written (one per chunk, assigned
+//     -- never accumulated), so a shorter call after a longer one cannot see stale partials.  The one region that must
+//     start at zero is the block of per-tensor completion counters the kernel counts its finished chunks in: every
+//     call clears the counters it is going to use (a cudaMemsetAsync on the caller's stream, no allocation) rather
+//     than trusting the previous call to have left them at zero.
 //   * Two calls whose GPU work overlaps (different streams, or different host threads) race on the array and produce
 //     garbage.  Calls on one stream are ordered by the stream and are safe.
 //   * The first call on a device looks up the array's device address (cudaGetSymbolAddress).  Make that first call
 //     before starting any stream capture.
+//   * No call may be issued on a stream that is being captured, the first or any later one: the table travels to the
+//     GPU through one host buffer that the next call overwrites, so a replayed copy would deliver some other call's
+//     table.  Such a call is refused with MT_ECAPTURE before anything is enqueued.
 #include <cstring>
 #include <mutex>
 
@@ -40,7 +45,8 @@ constexpr size_t kMaxTensors = MT_NOALLOC_MAX_TENSORS;
 constexpr size_t kMaxChunks = MT_NOALLOC_MAX_CHUNKS;
 // table region: tile_begin[(T+1) x u32, padded] + numel[T x i64] + ptrs[T x ptr]
 constexpr size_t kTableBytes = ((kMaxTensors + 1) * 4 + 15) / 16 * 16 + kMaxTensors * 8 + kMaxTensors * 8;
-constexpr size_t kPartialOff = (kTableBytes + 255) / 256 * 256;
+constexpr size_t kTicketOff = (kTableBytes + 255) / 256 * 256;  // completion counters, [T + 1] x u32 (norm_tile_done)
+constexpr size_t kPartialOff = (kTicketOff + (kMaxTensors + 1) * 4 + 255) / 256 * 256;
 constexpr size_t kBytes = kPartialOff + kMaxChunks * sizeof(float);
 
 // The working memory.  In host code this name is only a handle for the runtime, NOT a device address: it must go
@@ -94,6 +100,13 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
 
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    MT_CUDA_OK(cudaStreamIsCapturing(stream, &cap));
+    if (cap != cudaStreamCaptureStatusNone)
+        return set_error(MT_ECAPTURE, "%s: the stream is being captured; this entry point stages its tensor table through a "
+                         "shared host buffer and cannot be recorded into a graph -- call it outside the capture, or "
+                         "capture mt_multi_tensor_l2norm with caller-provided scratch instead", who);
+
     std::lock_guard<std::mutex> lk(g_mu);
     unsigned char* dev = nullptr;
     rc = resolve(tl->device, &dev);
@@ -114,6 +127,7 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     memcpy(g_host_table + off_ptrs, tl->ptrs, nt * 8);
     // pageable source: the runtime has consumed g_host_table when this returns, so the next call may overwrite it
     MT_CUDA_OK(cudaMemcpyAsync(dev, g_host_table, table_bytes, cudaMemcpyHostToDevice, stream));
+    MT_CUDA_OK(cudaMemsetAsync(dev + kTicketOff, 0, (nt + 1) * 4, stream));  // the counters must start at zero
 
     DevTable tb;
     tb.tile_begin = reinterpret_cast<const uint32_t*>(dev);
@@ -122,14 +136,17 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     tb.ntensors = (int32_t)nt;
     tb.ntiles = (uint32_t)nchunks;
     tb.tile_elems = chunk_size;
+    tb.tickets = reinterpret_cast<uint32_t*>(dev + kTicketOff);
     float* partials = reinterpret_cast<float*>(dev + kPartialOff);
 
-    constexpr int G = 8, U = 2, THREADS = 256, MINB = 4;  // same shape as mt_multi_tensor_l2norm
+    float* ret_pt = per_tensor ? ret_per_tensor : nullptr;
+    if (nchunks == 0) return launch_norm_finalize(tb, partials, 1, ret, ret_pt, tl->device, stream);  // all empty: zeros
+    constexpr int G = 8, THREADS = 256, MINB = 4;  // same kernel and launch shape as mt_multi_tensor_l2norm
     MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
+        constexpr int U = sizeof(Tx) == 4 ? 2 : 4;
         using Op = L2NormOp<Tx, false>;
-        typename Op::Params prm{partials};
+        typename Op::Params prm{NormOut{partials, ret, ret_pt}};
         rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
     })
-    if (rc) return rc;
-    return launch_norm_finalize(tb, partials, 1, ret, per_tensor ? ret_per_tensor : nullptr, tl->device, stream);
+    return rc;
 }

@@ -1,10 +1,12 @@
 // mt_api_norm.cu -- multi_tensor_l2norm / multi_tensor_l2norm_scale entry points and the norm finalize kernel.
 //
-// Pass 1 (table-driven grid, one tile == one reference chunk): per-tile sum of squares -> scratch partials[tile],
-// flag raised when a tile's partial is non-finite (the reference's per-chunk definition,
-// /root/reference/csrc/multi_tensor_l2norm_kernel.cu:103-104).
-// Pass 2 (norm_finalize_kernel): fixed-order reduction of the partials -> global norm and per-tensor norms.
-// Deterministic (no float atomics); replaces cleanup / cleanup_v3 (csrc/multi_tensor_l2norm_kernel.cu:198-237).
+// ONE launch per call (table-driven grid, one tile == one reference chunk): per-tile sum of squares ->
+// scratch partials[tile], flag raised when a tile's partial is non-finite (the reference's per-chunk definition,
+// /root/reference/csrc/multi_tensor_l2norm_kernel.cu:103-104); the CTA that completes a tensor / the launch reduces
+// the partials in a fixed order (norm_tile_done, mt_common.cuh) -> per-tensor norms and global norm.  Deterministic
+// (no float atomics); replaces cleanup / cleanup_v3 (csrc/multi_tensor_l2norm_kernel.cu:198-237), which are separate
+// launches in the reference.  norm_finalize_kernel is what remains of this library's own second launch: it serves the
+// degenerate all-tensors-empty call only.
 #include "mt_host.h"
 #include "mt_ops.cuh"
 
@@ -74,24 +76,30 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     if (per_tensor && !ret_per_tensor) return set_error(MT_EINVAL, "%s: per_tensor requested but ret_per_tensor is NULL", who);
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, chunk_size, stream, &tb);
     if (rc) return rc;
     const size_t need = (size_t)tb.ntiles * sizeof(float);
     if (need > 0 && (!scratch || scratch_bytes < need))
         return set_error(MT_ESCRATCH, "%s: scratch too small (%zu < %zu bytes)", who, scratch_bytes, need);
     float* partials = static_cast<float*>(scratch);
-    // 2 groups in flight per thread: a pure reduction has registers to spare
-    constexpr int G = 8, U = 2, THREADS = 256, MINB = 4;
+    float* ret_pt = per_tensor ? ret_per_tensor : nullptr;
+    if (tb.ntiles == 0)  // every tensor empty: zeros, by the small kernel (no tile exists to do it in-launch)
+        return launch_norm_finalize(tb, partials, 1, ret, ret_pt, tl->device, stream, mp ? noop_flag : nullptr);
+    const NormOut out{partials, ret, ret_pt};
+    // Bytes in flight per thread: 2 groups of 32 B for fp32, 4 groups of 16 B for the 16-bit types (a pure reduction
+    // has registers to spare, and 16-byte loads need twice the depth to cover the same latency).
+    constexpr int G = 8, THREADS = 256, MINB = 4;
     if (depth == 1) {
         MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
+            constexpr int U = sizeof(Tx) == 4 ? 2 : 4;
             if (mp) {
                 using Op = L2NormOp<Tx, true>;
-                typename Op::Params prm{partials};
+                typename Op::Params prm{out};
                 rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             } else {
                 using Op = L2NormOp<Tx, false>;
-                typename Op::Params prm{partials};
+                typename Op::Params prm{out};
                 rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             }
         })
@@ -99,13 +107,11 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
         MT_DISPATCH_FHB(tl->dtype[0], Tin, who,
             MT_DISPATCH_FHB(tl->dtype[1], Tout, who, {
                 using Op = L2NormScaleOp<Tin, Tout>;
-                typename Op::Params prm{partials, scale};
-                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+                typename Op::Params prm{out, scale};
+                rc = launch_table_kernel<Op, G, 2, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             }))
     }
-    if (rc) return rc;
-    return launch_norm_finalize(tb, partials, 1, ret, per_tensor ? ret_per_tensor : nullptr, tl->device, stream,
-                                mp ? noop_flag : nullptr);
+    return rc;
 }
 
 }  // namespace mt

@@ -1,13 +1,11 @@
 // mt_api_optim.cu -- optimizer entry points: Adam, mixed-precision (sharded) Adam, SGD, LAMB, legacy split LAMB.
 #include <cmath>
+#include <cstdlib>
 
 #include "mt_host.h"
 #include "mt_ops.cuh"
 
 namespace mt {
-
-int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, float* ret_global, float* ret_pt,
-                         int device, cudaStream_t stream, const int32_t* skip_if_set = nullptr);  // mt_api_norm.cu
 
 // Host-side bias corrections: /root/reference/csrc/multi_tensor_adam.cu:145-149.  std::pow(float, int)
 // promotes to double; the result is rounded to float.
@@ -18,6 +16,17 @@ static void bias_corrections(float beta1, float beta2, int step, int bias_correc
         *bc1 = (float)(1.0 - std::pow((double)beta1, (double)step));
         *bc2 = (float)(1.0 - std::pow((double)beta2, (double)step));
     }
+}
+
+// LAMB stage 1 keeps two norm accumulators live across the IEEE-division helper calls: under the 64-register cap of
+// 4 CTAs/SM ptxas spills them inside the element loop, at 80 registers (3 CTAs/SM) it does not
+// (profiles/r2_sass_summary.txt).  MT_LAMB_STAGE1_MINB=4 selects the old build for A/B timing.
+static bool lamb_stage1_wide() {
+    static const bool wide = [] {
+        const char* e = getenv("MT_LAMB_STAGE1_MINB");
+        return !(e && atoi(e) == 4);
+    }();
+    return wide;
 }
 
 static inline size_t align256(size_t x) { return (x + 255) / 256 * 256; }
@@ -56,25 +65,26 @@ extern "C" int mt_multi_tensor_adam(int chunk_size, int32_t* noop_flag, const Mt
             return set_error(MT_EINVAL, "multi_tensor_adam: g, p, m, v must share one dtype (as the reference assumes)");
     float bc1, bc2;
     bias_corrections(beta1, beta2, step, bias_correction, &bc1, &bc2);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
-#define MT_ADAM(CT)                                                                                       \
+    // (double lists: the 64-bit conversions need more registers than the 64 of 4 CTAs/SM leave -> 3 CTAs/SM, no spills)
+#define MT_ADAM(CT, MINB)                                                                                 \
     {                                                                                                     \
         if (mode == 0) {                                                                                  \
             using Op = AdamOp<CT, 0>;                                                                     \
             typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay};                   \
-            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+            return launch_table_kernel<Op, kG, kU, kThreads, MINB>(tb, prm, noop_flag, tl->device, stream); \
         }                                                                                                 \
         using Op = AdamOp<CT, 1>;                                                                         \
         typename Op::Params prm{beta1, beta2, bc1, bc2, epsilon, lr, weight_decay};                       \
-        return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream); \
+        return launch_table_kernel<Op, kG, kU, kThreads, MINB>(tb, prm, noop_flag, tl->device, stream);   \
     }
     switch (tl->dtype[0]) {
-        case MT_F32: MT_ADAM(float)
-        case MT_F16: MT_ADAM(__half)
-        case MT_BF16: MT_ADAM(__nv_bfloat16)
-        case MT_F64: MT_ADAM(double)
+        case MT_F32: MT_ADAM(float, kMinBlocks)
+        case MT_F16: MT_ADAM(__half, kMinBlocks)
+        case MT_BF16: MT_ADAM(__nv_bfloat16, kMinBlocks)
+        case MT_F64: MT_ADAM(double, 3)
         default: return set_error(MT_EINVAL, "multi_tensor_adam: unsupported dtype tag %d", tl->dtype[0]);
     }
 #undef MT_ADAM
@@ -99,7 +109,7 @@ static int fused_adam_impl(const char* who, int32_t* noop_flag, const MtTensorLi
         if (tl->dtype[d] != MT_F32) return set_error(MT_EINVAL, "%s: p, m, v must be float32", who);
     if (tl->depth == 5 && tl->dtype[4] != tl->dtype[3])
         return set_error(MT_EINVAL, "%s: p_copy must have the gradient dtype", who);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     const bool copy = tl->depth == 5;
@@ -152,7 +162,7 @@ extern "C" int mt_multi_tensor_sgd(int chunk_size, int32_t* noop_flag, const MtT
     if (tl->dtype[2] != wt) return set_error(MT_EINVAL, "multi_tensor_sgd: momentum dtype must equal the weight dtype");
     if (tl->depth == 4 && tl->dtype[3] != MT_F16)
         return set_error(MT_EINVAL, "Additional output tensors should always be fp16.");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
 #define MT_SGD(TG, TW, COPY)                                                                              \
@@ -195,7 +205,7 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
     bias_corrections(beta1, beta2, step, bias_correction, &bc1, &bc2);
     float beta3 = 1.0f;
     if (grad_averaging == 1) beta3 = 1 - beta1;  // csrc/multi_tensor_lamb.cu:363-364
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     const LambScratch lay = lamb_scratch_layout(tb.ntiles, tl->ntensors);
@@ -213,19 +223,18 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
         if (mode == 0) {
             using Op1 = LambStage1Op<Tp, 0>;
             typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
-                                    global_grad_norm, partials, tb.ntiles, mode, need_norms};
-            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+                                    global_grad_norm, NormOut{partials, nullptr, pnorm}, mode, need_norms};
+            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream)
+                                    : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
         } else {
             using Op1 = LambStage1Op<Tp, 1>;
             typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
-                                    global_grad_norm, partials, tb.ntiles, mode, need_norms};
-            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
+                                    global_grad_norm, NormOut{partials, nullptr, pnorm}, mode, need_norms};
+            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream)
+                                    : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
         }
         if (rc) return rc;
-        if (need_norms) {
-            rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream);
-            if (rc) return rc;
-        }
+        // (the per-tensor norms were finalized inside the stage-1 launch: norm_tile_done)
         // stage 2 walks lists [u (= g), p] of the SAME table: list indices 0 and 1
         using Op2 = LambStage2Op<Tp>;
         typename Op2::Params p2{pnorm, unorm, lr, weight_decay, use_nvlamb};
@@ -252,7 +261,7 @@ extern "C" int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const
     if (!copy && pt != gt) return set_error(MT_EINVAL, "multi_tensor_lamb_mp: with 4 lists all lists must share one dtype");
     float beta3 = 1.0f;
     if (grad_averaging == 1) beta3 = 1 - beta1;
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     const LambScratch lay = lamb_scratch_layout(tb.ntiles, tl->ntensors);
@@ -268,19 +277,17 @@ extern "C" int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const
         if (mode == 0) {                                                                                            \
             using Op1 = LambMpStage1Op<TG, TP, 0>;                                                                  \
             typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
-                                    max_grad_norm, inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms}; \
-            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);     \
+                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm}, mode, bias_correction, need_norms}; \
+            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
+                                    : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream); \
         } else {                                                                                                    \
             using Op1 = LambMpStage1Op<TG, TP, 1>;                                                                  \
             typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
-                                    max_grad_norm, inv_scale, partials, tb.ntiles, mode, bias_correction, need_norms}; \
-            rc = launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);     \
+                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm}, mode, bias_correction, need_norms}; \
+            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
+                                    : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream); \
         }                                                                                                           \
         if (rc) return rc;                                                                                          \
-        if (need_norms) {                                                                                           \
-            rc = launch_norm_finalize(tb, partials, 2, nullptr, pnorm, tl->device, stream, noop_flag);              \
-            if (rc) return rc;                                                                                      \
-        }                                                                                                           \
         using Op2 = LambMpStage2Op<TG, TP, COPY>;                                                                   \
         typename Op2::Params p2{pnorm, unorm, lr, weight_decay, use_nvlamb};                                        \
         return launch_table_kernel<Op2, kG, kU, kThreads, kMinBlocks>(tb, p2, noop_flag, tl->device, stream);       \
@@ -313,7 +320,7 @@ extern "C" int mt_multi_tensor_lamb_stage1(int chunk_size, int32_t* noop_flag, c
     const float next_step = (float)(step + 1);
     const float bc1 = 1.0f - std::pow(beta1, next_step);
     const float bc2 = 1.0f - std::pow(beta2, next_step);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[0], Tg, "lamb_stage_1",
@@ -332,7 +339,7 @@ extern "C" int mt_multi_tensor_lamb_stage2(int chunk_size, int32_t* noop_flag, c
     MT_PROLOGUE("multi_tensor_lamb_stage2_cuda", 2, 2)
     if (!per_tensor_param_norm || !per_tensor_update_norm)
         return set_error(MT_EINVAL, "multi_tensor_lamb_stage2_cuda: norm arrays are NULL");
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[0], Tp, "lamb_stage_2",

@@ -66,7 +66,7 @@ extern "C" int mt_multi_tensor_fused_adam_p2p(int chunk_size, int32_t* noop_flag
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     const bool mc = grad_multicast != nullptr;

@@ -12,7 +12,7 @@ extern "C" int mt_multi_tensor_scale(int chunk_size, int32_t* noop_flag, const M
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "multi_tensor_scale: cannot select CUDA device %d", tl->device);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[0], Tin, "multi_tensor_scale",
@@ -33,7 +33,7 @@ extern "C" int mt_multi_tensor_maybe_cast(int chunk_size, int32_t* noop_flag, co
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "maybe_cast_mt: cannot select CUDA device %d", tl->device);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[0], Tin, "maybe_cast_mt",
@@ -55,7 +55,7 @@ extern "C" int mt_multi_tensor_axpby(int chunk_size, int32_t* noop_flag, const M
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "multi_tensor_axpby: cannot select CUDA device %d", tl->device);
-    DevTable tb;
+    TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
     MT_DISPATCH_FHB(tl->dtype[0], Tx, "multi_tensor_axpby",

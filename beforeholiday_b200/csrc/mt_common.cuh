@@ -33,6 +33,9 @@ struct DevTable {
     int32_t ntensors;
     uint32_t ntiles;
     int32_t tile_elems;
+    // [ntensors + 1] completion counters of the reducing ops (per tensor; [ntensors] = whole launch).  Zero between
+    // launches: the CTA that takes the last ticket finalizes and puts the counter back to zero (norm_tile_done below).
+    uint32_t* tickets;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -253,6 +256,97 @@ template <int THREADS> __device__ __forceinline__ float block_sum(float v, float
 }
 
 // ------------------------------------------------------------------------------------------------
+// In-launch finalize of the reducing ops (replaces the reference's separate cleanup kernels,
+// /root/reference/csrc/multi_tensor_l2norm_kernel.cu:198-237, and this library's former second launch).
+//
+// Every tile leaves NSETS partial sums in scratch, then hands in a ticket for its tensor and one for the launch
+// (fence, atomicAdd).  The CTA holding a tensor's last ticket reduces that tensor's partials -- one warp, lanes striding
+// the tiles, fixed shuffle tree: the order does not depend on which CTA does it or when, so the result is
+// deterministic and bit-identical to the former finalize kernel -- and writes sqrt() to ret_pt.  The CTA holding the
+// launch's last ticket reduces ALL partials in the order of a 512-thread block_sum (two virtual threads per thread)
+// and writes ret_global.  Both put their counter back to zero, so the counters (DevTable::tickets) need no clearing
+// between launches, captured graph replays included.  Tensors without elements own no tile: the first tile of the next
+// tensor (or the last tile of the launch, for trailing ones) writes their zeros.
+struct NormOut {
+    float* partials;    // [NSETS][ntiles] scratch
+    float* ret_global;  // [NSETS] or NULL
+    float* ret_pt;      // [NSETS][ntensors] or NULL
+};
+
+template <int THREADS> constexpr int kSmemFloats = 512 / 32 + 4;
+
+template <int THREADS, int NSETS, bool kQuietWhenFlagged>
+__device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t, uint32_t tile, const NormOut& o,
+                                               float* smem, const int32_t* noop) {
+    static_assert(THREADS == 256, "the global reduction emulates a 512-thread block with two accumulators per thread");
+    unsigned* sflag = reinterpret_cast<unsigned*>(smem + 512 / 32);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        unsigned r = 0;
+        __threadfence();  // this tile's partials (and flag) before its tickets
+        if (o.ret_pt) {
+            const uint32_t b = __ldg(tb.tile_begin + t.tensor), e = __ldg(tb.tile_begin + t.tensor + 1);
+            if (atomicAdd(tb.tickets + t.tensor, 1u) + 1u == e - b) r |= 1u;
+            const bool quiet = kQuietWhenFlagged && *reinterpret_cast<const volatile int32_t*>(noop) != 0;
+            if (!quiet) {
+                if (t.start == 0)
+                    for (int k = t.tensor - 1; k >= 0 && __ldg(tb.tile_begin + k) == b; k--)
+                        for (int s = 0; s < NSETS; s++) o.ret_pt[(size_t)s * tb.ntensors + k] = 0.f;
+                if (tile == tb.ntiles - 1)
+                    for (int k = t.tensor + 1; k < tb.ntensors; k++)
+                        for (int s = 0; s < NSETS; s++) o.ret_pt[(size_t)s * tb.ntensors + k] = 0.f;
+            }
+        }
+        if (o.ret_global)
+            if (atomicAdd(tb.tickets + tb.ntensors, 1u) + 1u == tb.ntiles) r |= 2u;
+        if (r) __threadfence();  // everybody else's partials after the last ticket
+        *sflag = r;
+    }
+    __syncthreads();
+    const unsigned r = *sflag;
+    if (r == 0) return;  // uniform across the CTA
+    // "_mp" variants leave their outputs alone when the flag is up (csrc/multi_tensor_l2norm_kernel_mp.cu:121-123)
+    const bool quiet = kQuietWhenFlagged && *reinterpret_cast<const volatile int32_t*>(noop) != 0;
+    if ((r & 1u) && warp == 0) {
+        const uint32_t b = __ldg(tb.tile_begin + t.tensor), e = __ldg(tb.tile_begin + t.tensor + 1);
+#pragma unroll
+        for (int s = 0; s < NSETS; s++) {
+            const float* p = o.partials + (size_t)s * tb.ntiles;
+            float acc = 0.f;
+            for (uint32_t i = b + lane; i < e; i += 32) acc = fadd(acc, __ldcg(p + i));
+#pragma unroll
+            for (int k = 16; k > 0; k >>= 1) acc = fadd(acc, __shfl_xor_sync(0xffffffffu, acc, k));
+            if (lane == 0 && !quiet) o.ret_pt[(size_t)s * tb.ntensors + t.tensor] = fsqrt(acc);
+        }
+        if (lane == 0) tb.tickets[t.tensor] = 0u;
+    }
+    if (r & 2u) {
+#pragma unroll
+        for (int s = 0; s < NSETS; s++) {
+            const float* p = o.partials + (size_t)s * tb.ntiles;
+            float a0 = 0.f, a1 = 0.f;  // virtual threads tid and tid + 256 of a 512-thread block
+            for (uint32_t i = tid; i < tb.ntiles; i += 512) a0 = fadd(a0, __ldcg(p + i));
+            for (uint32_t i = tid + 256; i < tb.ntiles; i += 512) a1 = fadd(a1, __ldcg(p + i));
+#pragma unroll
+            for (int k = 16; k > 0; k >>= 1) {
+                a0 = fadd(a0, __shfl_xor_sync(0xffffffffu, a0, k));
+                a1 = fadd(a1, __shfl_xor_sync(0xffffffffu, a1, k));
+            }
+            __syncthreads();
+            if (lane == 0) { smem[warp] = a0; smem[warp + 8] = a1; }
+            __syncthreads();
+            if (warp == 0) {
+                float v = lane < 16 ? smem[lane] : 0.f;
+#pragma unroll
+                for (int k = 16; k > 0; k >>= 1) v = fadd(v, __shfl_xor_sync(0xffffffffu, v, k));
+                if (lane == 0 && !quiet) o.ret_global[s] = fsqrt(v);
+            }
+        }
+        if (tid == 0) tb.tickets[tb.ntensors] = 0u;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Op concept (all static / const, so everything inlines):
 //
 //   static constexpr int kLists;                 number of tensor lists
@@ -266,8 +360,10 @@ template <int THREADS> __device__ __forceinline__ float block_sum(float v, float
 //   __device__ void elem(float (&x)[kLists], State&);   one element: inputs in x, outputs written to x
 //   static constexpr unsigned kCustomLoad, kCustomStore;  + custom_load<D,G,kVec>() / custom_store<D,G,kVec>()
 //                                                (lists the Op moves itself, e.g. over NVLink peer pointers)
-//   template <int THREADS> __device__ void end_tile_n(uint32_t tile, State&, float* smem, int32_t* noop);
-//                                                (norm ops: block reduce + per-tile partial + flag)
+//   template <int THREADS> __device__ void end_tile_n(const DevTable&, const Tile&, uint32_t tile, State&, float* smem,
+//                                                     int32_t* noop, bool skipped);
+//                                                (norm ops: block reduce + per-tile partial + flag + finalize ticket)
+//   static constexpr bool kTickets;              the op finalizes in-launch (norm_tile_done): early-exiting CTAs still tick
 //   __device__ void finish(State&, int32_t* noop);                  (flag ops)
 //
 template <class Op, int D> using ListT = typename Op::template T<D>;
@@ -410,9 +506,15 @@ __device__ __forceinline__ void fetch_bases(const DevTable& tb, int tensor, char
 template <class Op, int G, int U, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __restrict__ noop) {
-    __shared__ float smem[THREADS / 32];
+    __shared__ float smem[kSmemFloats<THREADS>];
+    bool skipped = false;
     if (Op::kEarlyExit) {
-        if (*reinterpret_cast<volatile int32_t*>(noop) != 0) return;
+        if (*reinterpret_cast<volatile int32_t*>(noop) != 0) {
+            // Ops that finalize through completion tickets must still hand their tickets in, or the counters would
+            // not return to zero; everything else simply leaves.
+            if (!Op::kTickets) return;
+            skipped = true;
+        }
     }
     Op op(prm);
     typename Op::State st;
@@ -420,11 +522,13 @@ mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __res
     using Seq = std::make_integer_sequence<int, Op::kLists>;
     for (uint32_t tile = blockIdx.x; tile < tb.ntiles; tile += gridDim.x) {
         const Tile t = locate_tile(tb, tile);
-        char* base[Op::kLists];
-        fetch_bases<Op>(tb, t.tensor, base, Seq{});
-        op.begin_tensor(t.tensor);
-        process_tile<Op, G, U, THREADS>(op, base, t, st);
-        op.template end_tile_n<THREADS>(tile, st, smem, noop);
+        if (!skipped) {
+            char* base[Op::kLists];
+            fetch_bases<Op>(tb, t.tensor, base, Seq{});
+            op.begin_tensor(t.tensor);
+            process_tile<Op, G, U, THREADS>(op, base, t, st);
+        }
+        op.template end_tile_n<THREADS>(tb, t, tile, st, smem, noop, skipped);
     }
     op.finish(st, noop);
 }
@@ -439,7 +543,9 @@ struct OpBase {
     __device__ __forceinline__ void begin_tensor(int) {}
     __device__ __forceinline__ bool load(int) const { return true; }
     __device__ __forceinline__ bool store(int) const { return true; }
-    template <int THREADS, class S> __device__ __forceinline__ void end_tile_n(uint32_t, S&, float*, int32_t*) const {}
+    static constexpr bool kTickets = false;  // finalizes inside the launch through DevTable::tickets (norm_tile_done)
+    template <int THREADS, class S>
+    __device__ __forceinline__ void end_tile_n(const DevTable&, const Tile&, uint32_t, S&, float*, int32_t*, bool) const {}
     template <class S> __device__ __forceinline__ void finish(S&, int32_t*) const {}
 };
 

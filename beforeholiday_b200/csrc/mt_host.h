@@ -54,9 +54,24 @@ int64_t total_elems(const MtTensorLists* tl);
 int choose_tile_elems(const MtTensorLists* tl, int device);
 uint64_t count_tiles(const MtTensorLists* tl, int tile_elems);
 
+// A cached table as one call holds it: the DevTable the kernels take (pass it by value -- it slices) plus a lease on
+// the cache entry.  release() (run by the destructor, i.e. behind the call's last launch) records the entry's
+// "last use" event on the call's stream; eviction only ever takes entries whose events have completed.
+struct TableRef : DevTable {
+    TableRef() : DevTable{} {}
+    TableRef(const TableRef&) = delete;
+    TableRef& operator=(const TableRef&) = delete;
+    ~TableRef() { release(); }
+    void release();
+    void* entry_ = nullptr;
+    int slot_ = -1, device_ = 0;
+    cudaStream_t stream_ = nullptr;
+};
+
 // Look the (lists, tile_elems) pair up in the per-device table cache; on a miss build the table, upload it
 // (one cudaMemcpyAsync on `stream`) and cache it.  Steady-state steps with unchanged pointers upload nothing.
-int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevTable* out);
+// A hit from a stream other than the uploading one is ordered behind the upload (see mt_table.cu).
+int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, TableRef* out);
 
 // ---- launcher -------------------------------------------------------------------------------------
 // One CTA per tile (see mt_common.cuh for the measurements behind this choice).  gridDim.x can hold 2^31-1 tiles,

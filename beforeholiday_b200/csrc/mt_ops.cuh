@@ -323,30 +323,37 @@ struct SumState { float sum; };
 template <class Tx, bool kMp = false> struct L2NormOp : OpBase {
     static constexpr int kLists = 1;
     static constexpr bool kEarlyExit = kMp;
+    static constexpr bool kTickets = true;
     template <int D> using T = Tx;
     static constexpr unsigned kRead = 0b1, kWrite = 0b0;
-    struct Params { float* partials; };
+    struct Params { NormOut out; };
     using State = SumState;
     Params p;
     __device__ explicit L2NormOp(const Params& q) : p(q) {}
     __device__ __forceinline__ void init(State& s) const { s.sum = 0.f; }
     __device__ __forceinline__ void elem(float (&x)[1], State& s) const { s.sum = fadd(s.sum, fmul(x[0], x[0])); }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
-        const float tot = block_sum<THREADS>(s.sum, smem);
-        if (threadIdx.x == 0) {
-            p.partials[tile] = tot;
-            if (!finite_f(tot)) *noop = 1;
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable& tb, const Tile& t, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool skipped) const {
+        if (!skipped) {
+            const float tot = block_sum<THREADS>(s.sum, smem);
+            if (threadIdx.x == 0) {
+                p.out.partials[tile] = tot;
+                if (!finite_f(tot)) *noop = 1;
+            }
         }
         s.sum = 0.f;
+        norm_tile_done<THREADS, 1, kMp>(tb, t, tile, p.out, smem, noop);
     }
 };
 
 // L2NormScaleFunctor: csrc/multi_tensor_l2norm_scale_kernel.cu:79-81,127-131.   lists: in, out
 template <class Tin, class Tout> struct L2NormScaleOp : OpBase {
     static constexpr int kLists = 2;
+    static constexpr bool kTickets = true;
     template <int D> using T = typename Types<Tin, Tout>::template at<D>;
     static constexpr unsigned kRead = 0b01, kWrite = 0b10;
-    struct Params { float* partials; float scale; };
+    struct Params { NormOut out; float scale; };
     using State = SumState;
     Params p;
     __device__ explicit L2NormScaleOp(const Params& q) : p(q) {}
@@ -355,13 +362,16 @@ template <class Tin, class Tout> struct L2NormScaleOp : OpBase {
         s.sum = fadd(s.sum, fmul(x[0], x[0]));
         x[1] = fmul(x[0], p.scale);
     }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable& tb, const Tile& t, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool) const {
         const float tot = block_sum<THREADS>(s.sum, smem);
         if (threadIdx.x == 0) {
-            p.partials[tile] = tot;
+            p.out.partials[tile] = tot;
             if (!finite_f(tot)) *noop = 1;
         }
         s.sum = 0.f;
+        norm_tile_done<THREADS, 1, false>(tb, t, tile, p.out, smem, noop);
     }
 };
 
@@ -378,11 +388,11 @@ template <class Tp, int kMode> struct LambStage1Op : OpBase {
     struct Params {
         float beta1, beta2, beta3, bc1, bc2, eps, decay, max_grad_norm;
         const float* global_grad_norm;
-        float* partials;      // [2][ntiles]: p^2 then u^2
-        uint32_t ntiles;
+        NormOut out;          // partials [2][ntiles]: p^2 then u^2; ret_pt [2][ntensors]: ||p|| then ||u||
         int mode, need_norms;
     };
     using State = Sum2State;
+    static constexpr bool kTickets = true;
     Params p;
     float clip, omb2;
     __device__ explicit LambStage1Op(const Params& q) : p(q), omb2(fsub(1.f, q.beta2)) {
@@ -408,13 +418,16 @@ template <class Tp, int kMode> struct LambStage1Op : OpBase {
         s.su = fadd(s.su, fmul(ur, ur));
         x[0] = u; x[2] = m; x[3] = v;
     }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t*) const {
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable& tb, const Tile& t, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool) const {
         if (p.need_norms) {  // uniform
             const float tp = block_sum<THREADS>(s.sp, smem);
             const float tu = block_sum<THREADS>(s.su, smem);
-            if (threadIdx.x == 0) { p.partials[tile] = tp; p.partials[p.ntiles + tile] = tu; }
+            if (threadIdx.x == 0) { p.out.partials[tile] = tp; p.out.partials[tb.ntiles + tile] = tu; }
+            s.sp = 0.f; s.su = 0.f;
+            norm_tile_done<THREADS, 2, false>(tb, t, tile, p.out, smem, noop);
         }
-        s.sp = 0.f; s.su = 0.f;
     }
 };
 
@@ -451,11 +464,11 @@ template <class Tg, class Tp, int kMode> struct LambMpStage1Op : OpBase {
         float beta1, beta2, beta3, eps, decay;
         const int32_t* step;
         const float *global_grad_norm, *max_grad_norm, *inv_scale;
-        float* partials;  // [2][ntiles]
-        uint32_t ntiles;
+        NormOut out;  // partials [2][ntiles], ret_pt [2][ntensors]
         int mode, bias_correction, need_norms;
     };
     using State = Sum2State;
+    static constexpr bool kTickets = true;
     Params p;
     float clip, omb2, bc1, bc2, inv_scale;
     __device__ explicit LambMpStage1Op(const Params& q) : p(q), omb2(fsub(1.f, q.beta2)), bc1(1.f), bc2(1.f) {
@@ -486,13 +499,18 @@ template <class Tg, class Tp, int kMode> struct LambMpStage1Op : OpBase {
         s.su = fadd(s.su, fmul(ur, ur));
         x[0] = u; x[2] = m; x[3] = v;
     }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t*) const {
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable& tb, const Tile& t, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool skipped) const {
         if (p.need_norms) {
-            const float tp = block_sum<THREADS>(s.sp, smem);
-            const float tu = block_sum<THREADS>(s.su, smem);
-            if (threadIdx.x == 0) { p.partials[tile] = tp; p.partials[p.ntiles + tile] = tu; }
+            if (!skipped) {
+                const float tp = block_sum<THREADS>(s.sp, smem);
+                const float tu = block_sum<THREADS>(s.su, smem);
+                if (threadIdx.x == 0) { p.out.partials[tile] = tp; p.out.partials[tb.ntiles + tile] = tu; }
+            }
+            s.sp = 0.f; s.su = 0.f;
+            norm_tile_done<THREADS, 2, true>(tb, t, tile, p.out, smem, noop);
         }
-        s.sp = 0.f; s.su = 0.f;
     }
 };
 
@@ -597,7 +615,9 @@ template <class Tx> struct MaxNormOp : OpBase {
     __device__ explicit MaxNormOp(const Params& q) : p(q) {}
     __device__ __forceinline__ void init(State& s) const { s.mx = 0.f; }
     __device__ __forceinline__ void elem(float (&x)[1], State& s) const { s.mx = fmaxf(fabsf(s.mx), fabsf(x[0])); }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable&, const Tile&, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool) const {
         const float tot = block_max<THREADS>(s.mx, smem);
         if (threadIdx.x == 0) {
             p.partials[tile] = tot;
@@ -758,7 +778,9 @@ template <class Tg, class Tn, int kMode> struct DistLambStage1Op : OpBase {
         s.su = fadd(s.su, fmul(u, u));
         x[4] = u; x[2] = m; x[3] = v;
     }
-    template <int THREADS> __device__ __forceinline__ void end_tile_n(uint32_t tile, State& s, float* smem, int32_t* noop) const {
+    template <int THREADS>
+    __device__ __forceinline__ void end_tile_n(const DevTable&, const Tile&, uint32_t tile, State& s, float* smem,
+                                               int32_t* noop, bool) const {
         if (p.need_norms) {
             const float tp = block_sum<THREADS>(s.sp, smem);
             const float tu = block_sum<THREADS>(s.su, smem);

@@ -6,6 +6,7 @@
 // >=1042 for 50k small tensors).  Here the table lives in device memory, is built once per distinct
 // (pointer set, sizes, tile size) and is found again by hash, so a steady-state optimizer step uploads nothing
 // and issues ONE launch per op.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -111,7 +112,22 @@ int choose_tile_elems(const MtTensorLists* tl, int device) {
 }
 
 // ---- table cache --------------------------------------------------------------------------------
+//
+// Ordering rules (all under the per-device mutex; none of them ever synchronises the device):
+//   * upload   every Entry owns an event recorded right behind its cudaMemcpyAsync.  A hit from ANOTHER stream makes
+//              that stream wait on the event (cudaStreamWaitEvent) until the event has been seen complete once; the
+//              uploading stream itself is ordered by the stream.  A capturing stream cannot wait on an event recorded
+//              outside its capture, so there the host waits for the upload instead (once).
+//   * last use TableRef's destructor records a per-(entry, stream) event behind the call's last launch (kUseSlots
+//              slots; when more distinct streams than slots use one table, the newcomer is first made to wait on the
+//              slot it takes over, so that its own event covers the displaced use transitively).
+//   * eviction least-recently-used first, and only entries whose upload and use events have all completed; an entry
+//              that is still in flight (or referenced by a stream capture) is skipped, the cap is soft.  Blobs come
+//              from the stream-ordered allocator (cudaMallocAsync / cudaFreeAsync): unlike cudaMalloc / cudaFree these
+//              neither synchronise the device nor count as unsafe calls while another thread captures a graph.
 namespace {
+
+constexpr int kUseSlots = 4;
 
 struct Entry {
     std::vector<uint8_t> host;  // exact blob, for collision-proof comparison
@@ -119,6 +135,15 @@ struct Entry {
     size_t bytes = 0;
     uint32_t ntiles = 0;
     bool in_graph = false;  // referenced by a stream capture: never evicted
+    uint64_t tick = 0;      // LRU clock value of the last hit
+    cudaEvent_t upload_ev = nullptr;
+    cudaStream_t upload_stream = nullptr;
+    bool upload_done = false;
+    cudaStream_t use_stream[kUseSlots] = {};
+    cudaEvent_t use_ev[kUseSlots] = {};
+    bool use_live[kUseSlots] = {};
+    int use_next = 0;  // round-robin victim when every slot belongs to another stream
+    int leased = 0;    // calls between get_table() and TableRef::release(): their launches are not covered by an event yet
 };
 
 struct DeviceCache {
@@ -127,7 +152,7 @@ struct DeviceCache {
     // Most-recently-used entries, checked before anything is hashed: a training loop cycles through a handful of
     // (op, lists) pairs, and comparing the caller's pointer / numel arrays straight against a cached blob is one
     // memcmp pass instead of blob build (a 64-bit division per tensor) + hash + memcmp.  Pointers into `map` nodes
-    // (stable until erased; cleared on eviction).
+    // (stable until erased; an evicted entry is removed from this list first).
     static constexpr int kMru = 16;
     Entry* mru[kMru] = {};
     int mru_n = 0;
@@ -135,13 +160,21 @@ struct DeviceCache {
     size_t staging_cap = 0;
     cudaEvent_t staging_ev = nullptr;
     bool staging_pending = false;
+    uint64_t clock = 0;
     MtCacheStats stats{};
 };
 
 DeviceCache g_cache[64];
 
-constexpr size_t kMaxEntries = 1024;
-constexpr size_t kMaxDeviceBytes = 1ull << 30;
+// Soft caps (MT_TABLE_CACHE_MAX_ENTRIES / MT_TABLE_CACHE_MAX_BYTES override them; the tests use tiny values).
+size_t env_or(const char* name, size_t dflt) {
+    const char* e = getenv(name);
+    if (!e || !*e) return dflt;
+    const long long v = atoll(e);
+    return v > 0 ? (size_t)v : dflt;
+}
+size_t max_entries() { static const size_t v = env_or("MT_TABLE_CACHE_MAX_ENTRIES", 1024); return v; }
+size_t max_device_bytes() { static const size_t v = env_or("MT_TABLE_CACHE_MAX_BYTES", 1ull << 30); return v; }
 
 inline uint64_t mix64(uint64_t h, uint64_t v) {
     h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
@@ -174,16 +207,65 @@ uint64_t hash_blob(const uint8_t* p, size_t n) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+inline void mru_drop(DeviceCache& c, const Entry* e) {
+    int w = 0;
+    for (int i = 0; i < c.mru_n; i++)
+        if (c.mru[i] != e) c.mru[w++] = c.mru[i];
+    c.mru_n = w;
+}
+
+// Has every piece of GPU work that may still read this entry's blob finished?  (Queries only -- never blocks.)
+bool entry_idle(Entry& e) {
+    if (e.leased > 0) return false;
+    if (!e.upload_done) {
+        if (cudaEventQuery(e.upload_ev) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+        e.upload_done = true;
+    }
+    for (int i = 0; i < kUseSlots; i++)
+        if (e.use_live[i]) {
+            if (cudaEventQuery(e.use_ev[i]) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+            e.use_live[i] = false;
+        }
+    return true;
+}
+
+void destroy_entry(DeviceCache& c, Entry& e, cudaStream_t free_stream) {
+    mru_drop(c, &e);
+    if (e.dev) cudaFreeAsync(e.dev, free_stream);
+    if (e.upload_ev) cudaEventDestroy(e.upload_ev);
+    for (int i = 0; i < kUseSlots; i++)
+        if (e.use_ev[i]) cudaEventDestroy(e.use_ev[i]);
+    c.stats.device_bytes -= e.bytes;
+}
+
+// Make room for `incoming` more bytes: drop idle entries, oldest first, until the cache is back under 3/4 of its caps.
+// Entries that are in flight or captured stay; if nothing can go the caps are simply exceeded for a while.
+void evict_lru_locked(DeviceCache& c, size_t incoming, cudaStream_t stream) {
+    const size_t want_entries = max_entries() * 3 / 4, want_bytes = max_device_bytes() * 3 / 4;
+    std::vector<std::pair<uint64_t, decltype(c.map)::iterator>> order;
+    order.reserve(c.map.size());
+    for (auto it = c.map.begin(); it != c.map.end(); ++it)
+        if (!it->second.in_graph) order.emplace_back(it->second.tick, it);
+    std::sort(order.begin(), order.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+    for (auto& o : order) {
+        if (c.map.size() < want_entries && c.stats.device_bytes + incoming <= want_bytes) break;
+        Entry& e = o.second->second;
+        if (!entry_idle(e)) continue;
+        destroy_entry(c, e, stream);
+        c.map.erase(o.second);
+        c.stats.evictions++;
+    }
+    c.stats.entries = c.map.size();
+}
+
+// Everything goes (mt_table_cache_clear: an explicit request, documented to wait for the device).
 int evict_all_locked(DeviceCache& c) {
-    // rare path: the cache outgrew its caps.  In-flight kernels may still read the tables -> full sync first.
     MT_CUDA_OK(cudaDeviceSynchronize());
     for (auto it = c.map.begin(); it != c.map.end();) {
         if (it->second.in_graph) { ++it; continue; }
-        cudaFree(it->second.dev);
-        c.stats.device_bytes -= it->second.bytes;
+        destroy_entry(c, it->second, nullptr);
         it = c.map.erase(it);
     }
-    c.mru_n = 0;
     c.stats.entries = c.map.size();
     return MT_OK;
 }
@@ -200,8 +282,55 @@ inline void mru_touch(DeviceCache& c, Entry* e) {
     c.mru[0] = e;
 }
 
-inline void fill_out(const Entry* e, size_t nt, int tile_elems, size_t off_tb, size_t off_numel, size_t off_ptrs,
-                     DevTable* out) {
+// A cache hit on `stream`: order the stream behind the upload, pick the use slot this call will record into.
+int acquire_locked(DeviceCache& c, Entry* e, cudaStream_t stream, bool capturing, int* slot_out) {
+    e->tick = ++c.clock;
+    *slot_out = -1;
+    if (!e->upload_done) {
+        if (cudaEventQuery(e->upload_ev) == cudaSuccess) {
+            e->upload_done = true;
+        } else {
+            (void)cudaGetLastError();
+            if (capturing) {  // an event recorded outside the capture cannot be waited on inside it
+                MT_CUDA_OK(cudaEventSynchronize(e->upload_ev));
+                e->upload_done = true;
+            } else if (stream != e->upload_stream) {
+                MT_CUDA_OK(cudaStreamWaitEvent(stream, e->upload_ev, 0));
+                c.stats.cross_stream_waits++;
+            }
+        }
+    }
+    if (capturing) {
+        e->in_graph = true;  // pinned for good: replays may come at any time
+        return MT_OK;
+    }
+    int slot = -1;
+    for (int i = 0; i < kUseSlots && slot < 0; i++)
+        if (e->use_ev[i] && e->use_stream[i] == stream) slot = i;
+    for (int i = 0; i < kUseSlots && slot < 0; i++)
+        if (!e->use_ev[i]) slot = i;
+    if (slot < 0) {  // every slot belongs to another stream: take one over, inheriting what it guards
+        for (int k = 0; k < kUseSlots && slot < 0; k++) {
+            const int i = (e->use_next + k) % kUseSlots;
+            if (!e->use_live[i] || cudaEventQuery(e->use_ev[i]) == cudaSuccess) { e->use_live[i] = false; slot = i; }
+        }
+        (void)cudaGetLastError();
+        if (slot < 0) {
+            slot = e->use_next;
+            MT_CUDA_OK(cudaStreamWaitEvent(stream, e->use_ev[slot], 0));
+            c.stats.cross_stream_waits++;
+        }
+        e->use_next = (slot + 1) % kUseSlots;
+    }
+    if (!e->use_ev[slot]) MT_CUDA_OK(cudaEventCreateWithFlags(&e->use_ev[slot], cudaEventDisableTiming));
+    e->use_stream[slot] = stream;
+    e->leased++;
+    *slot_out = slot;
+    return MT_OK;
+}
+
+inline void fill_out(Entry* e, int device, cudaStream_t stream, int slot, size_t nt, int tile_elems, size_t off_tb,
+                     size_t off_numel, size_t off_ptrs, TableRef* out) {
     const uint8_t* d = static_cast<const uint8_t*>(e->dev);
     out->tile_begin = reinterpret_cast<const uint32_t*>(d + off_tb);
     out->numel = reinterpret_cast<const int64_t*>(d + off_numel);
@@ -209,15 +338,35 @@ inline void fill_out(const Entry* e, size_t nt, int tile_elems, size_t off_tb, s
     out->ntensors = (int32_t)nt;
     out->ntiles = e->ntiles;
     out->tile_elems = tile_elems;
+    out->tickets = reinterpret_cast<uint32_t*>(const_cast<uint8_t*>(d) + align_up(e->bytes, 16));
+    out->entry_ = slot >= 0 ? e : nullptr;
+    out->slot_ = slot;
+    out->device_ = device;
+    out->stream_ = stream;
 }
 
 }  // namespace
 
-int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevTable* out) {
+// End of a call that used a cached table: mark "last use" on its stream, behind everything the call launched.
+void TableRef::release() {
+    if (!entry_) return;
+    Entry* e = static_cast<Entry*>(entry_);
+    entry_ = nullptr;
+    DeviceCache& c = g_cache[device_];
+    std::lock_guard<std::mutex> lk(c.mu);
+    // (the entry cannot have been evicted since get_table(): `leased` kept it off the eviction list)
+    e->leased--;
+    if (cudaEventRecord(e->use_ev[slot_], stream_) == cudaSuccess) e->use_live[slot_] = true;
+    else (void)cudaGetLastError();
+}
+
+
+int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, TableRef* out) {
     const int device = tl->device;
     if (device < 0 || device >= 64) return set_error(MT_EINVAL, "device ordinal %d out of range", device);
     const size_t nt = (size_t)tl->ntensors;
     const int depth = tl->depth;
+    out->release();
 
     // blob layout (device and host identical):
     //   [0]                 header: depth, tile_elems (part of the key)
@@ -244,9 +393,11 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
             if (memcmp(hb + off_ptrs, tl->ptrs, (size_t)depth * nt * 8) != 0) continue;
             if (memcmp(hb + off_numel, tl->numel, nt * 8) != 0) continue;
             c.stats.hits++;
-            if (capturing) e->in_graph = true;
+            int slot;
+            const int rc = acquire_locked(c, e, stream, capturing, &slot);
+            if (rc) return rc;
             if (i) mru_touch(c, e);
-            fill_out(e, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
+            fill_out(e, device, stream, slot, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
             return MT_OK;
         }
     }
@@ -286,17 +437,14 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
         }
     if (e) {
         c.stats.hits++;
-        if (capturing) e->in_graph = true;
     } else {
         c.stats.misses++;
         if (capturing)
             return set_error(MT_ECAPTURE,
                              "device tensor-table cache miss while the stream is being captured; run the same call "
                              "once eagerly (warm-up) before capture so the table is resident");
-        if (c.map.size() >= kMaxEntries || c.stats.device_bytes + bytes > kMaxDeviceBytes) {
-            int rc = evict_all_locked(c);
-            if (rc) return rc;
-        }
+        if (c.map.size() >= max_entries() || c.stats.device_bytes + bytes > max_device_bytes())
+            evict_lru_locked(c, bytes, stream);
         // staging: one pinned buffer per device, reused once the previous upload has drained
         if (!c.staging_ev) MT_CUDA_OK(cudaEventCreateWithFlags(&c.staging_ev, cudaEventDisableTiming));
         if (c.staging_pending) {
@@ -312,26 +460,39 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, DevT
             c.staging_cap = cap_bytes;
         }
         Entry ne;
-        MT_CUDA_OK(cudaMalloc(&ne.dev, bytes));
-        memcpy(c.staging, blob.data(), bytes);
-        cudaError_t ce = cudaMemcpyAsync(ne.dev, c.staging, bytes, cudaMemcpyHostToDevice, stream);
-        if (ce == cudaSuccess) ce = cudaEventRecord(c.staging_ev, stream);
+        MT_CUDA_OK(cudaEventCreateWithFlags(&ne.upload_ev, cudaEventDisableTiming));
+        // device copy = blob + the completion counters of the reducing ops ([nt + 1] uint32, zero; see norm_tile_done)
+        const size_t off_tickets = align_up(bytes, 16), dev_bytes = off_tickets + (nt + 1) * 4;
+        cudaError_t ce = cudaMallocAsync(&ne.dev, dev_bytes, stream);
+        if (ce == cudaSuccess) {
+            memcpy(c.staging, blob.data(), bytes);
+            ce = cudaMemcpyAsync(ne.dev, c.staging, bytes, cudaMemcpyHostToDevice, stream);
+            if (ce == cudaSuccess)
+                ce = cudaMemsetAsync(static_cast<uint8_t*>(ne.dev) + off_tickets, 0, dev_bytes - off_tickets, stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(ne.upload_ev, stream);
+            if (ce == cudaSuccess) ce = cudaEventRecord(c.staging_ev, stream);
+        }
         if (ce != cudaSuccess) {
-            cudaFree(ne.dev);
+            if (ne.dev) cudaFreeAsync(ne.dev, stream);
+            cudaEventDestroy(ne.upload_ev);
             return set_error(MT_ECUDA, "table upload failed: %s", cudaGetErrorString(ce));
         }
         c.staging_pending = true;
+        ne.upload_stream = stream;
         ne.host = blob;
         ne.bytes = bytes;
         ne.ntiles = ntiles;
         c.stats.uploads_bytes += bytes;
-        c.stats.device_bytes += bytes;
+        c.stats.device_bytes += bytes;  // (the few counter bytes behind the blob are not itemised)
         auto it = c.map.emplace(h, std::move(ne));
         c.stats.entries = c.map.size();
         e = &it->second;
     }
+    int slot;
+    const int rc = acquire_locked(c, e, stream, capturing, &slot);
+    if (rc) return rc;
     mru_touch(c, e);
-    fill_out(e, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
+    fill_out(e, device, stream, slot, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
     return MT_OK;
 }
 

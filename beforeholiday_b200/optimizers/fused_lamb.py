@@ -102,13 +102,13 @@ class FusedLAMB(torch.optim.Optimizer):
             self._fast_norm_lists = (key, p32, p16, all_sets)
         _, p32, p16, _ = self._fast_norm_lists
         try:
-            n32 = self.multi_tensor_l2norm(65536, flag, [p32], False, grads_of=0)[0] if p32 else torch.zeros(1, device=device)
-            n16 = self.multi_tensor_l2norm(65536, flag, [p16], False, grads_of=0)[0] if p16 else torch.zeros(1, device=device)
+            n32 = self.multi_tensor_l2norm(65536, flag, [p32], False, grads_of=0)[0] if p32 else None
+            n16 = self.multi_tensor_l2norm(65536, flag, [p16], False, grads_of=0)[0] if p16 else None
         except RuntimeError as e:
             if not is_fallback(e):
                 raise
             return False            # norms only read: nothing to undo
-        global_grad_norm = self.multi_tensor_l2norm(65536, flag, [[n32, n16]], False)[0]
+        global_grad_norm = self._blend(n32, n16, device)
         max_grad_norm = self.defaults['max_grad_norm']
         for group, sets in zip(self.param_groups, all_sets):
             bias_correction = 1 if group['bias_correction'] else 0
@@ -123,6 +123,18 @@ class FusedLAMB(torch.optim.Optimizer):
                                        grads_of=0)
         return True
 
+    def _blend(self, n32, n16, device):
+        """sqrt(n32^2 + n16^2) on the device, as the reference does with a third l2norm call over [n32, n16]
+        (fused_lamb.py:131-135).  With one dtype only there is nothing to blend: sqrt(x*x) == x exactly in binary
+        floating point, so the lone norm IS the blended value and the extra launch is skipped."""
+        if n32 is None and n16 is None:
+            return torch.zeros(1, device=device)
+        if n16 is None:
+            return n32
+        if n32 is None:
+            return n16
+        return self.multi_tensor_l2norm(65536, self._dummy_overflow_buf, [[n32, n16]], False)[0]
+
     def _global_grad_norm(self):
         g32, g16 = [], []
         for group in self.param_groups:
@@ -136,14 +148,12 @@ class FusedLAMB(torch.optim.Optimizer):
                 else:
                     raise RuntimeError('FusedLAMB only support fp16 and fp32.')
         device = self.param_groups[0]["params"][0].device
-        n32 = torch.zeros(1, device=device)
-        n16 = torch.zeros(1, device=device)
+        n32 = n16 = None
         if g32:
             n32 = multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g32], False)[0]
         if g16:
             n16 = multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [g16], False)[0]
-        # blend: sqrt(n32^2 + n16^2), on the device
-        return multi_tensor_applier_l2norm(self.multi_tensor_l2norm, self._dummy_overflow_buf, [[n32, n16]], False)[0]
+        return self._blend(n32, n16, device)
 
     def step(self, closure=None):
         loss = None

@@ -104,13 +104,23 @@ def unflatten(coalesced: torch.Tensor, bucket: Sequence[torch.Tensor]):
 
 def apply_flat_dist_call(bucket, call, extra_args=None):
     """flatten -> call(coalesced, *extra_args) -> (average if call is all_reduce) -> copy back (:36-49).  The average
-    rides on the copy back, which is one launch."""
+    rides on the copy back, which is one launch for every tensor that is contiguous in the default layout.  A tensor in
+    another dense layout (channels_last weights, transposed views) was flattened in LOGICAL order by `flatten`, and
+    `reshape(-1)` of it is a temporary, so it is written back through `copy_` on a shaped view of the coalesced buffer,
+    as the reference does for every tensor (`buf.copy_(synced)`, :48-49)."""
     bucket = list(bucket)
     coalesced = flatten(bucket)
     call(coalesced, *(extra_args or ()))
     post = 1.0 / dist.get_world_size() if call is dist.all_reduce else 1.0
-    flag = torch.zeros(1, dtype=torch.int32, device=coalesced.device)
-    multi_tensor_applier(_amp_scale(), flag, [list(_views(coalesced, bucket)), [t.reshape(-1) for t in bucket]], post)
+    views = list(_views(coalesced, bucket))
+    src = [v for v, t in zip(views, bucket) if t.is_contiguous()]
+    dst = [t.view(-1) for t in bucket if t.is_contiguous()]
+    if src:
+        flag = torch.zeros(1, dtype=torch.int32, device=coalesced.device)
+        multi_tensor_applier(_amp_scale(), flag, [src, dst], post)
+    for v, t in zip(views, bucket):
+        if not t.is_contiguous():
+            t.copy_(v.view(t.shape) if post == 1.0 else v.view(t.shape) * post)
 
 
 def split_by_type(tensors):

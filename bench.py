@@ -11,7 +11,11 @@ One JSON line on stdout (rank 0).  A "step" is one optimizer step over one synth
           apex/contrib/csrc/optimizers/multi_tensor_distopt_adam.cpp:3-19).
   N > 1   the same parameter set with the optimizer state sharded ZeRO-2 style over N ranks
           (beforeholiday_b200.contrib.optimizers.DistributedFusedAdam): reduce-scatter bf16 grads -> shard update ->
-          all-gather bf16 params.  Total work is fixed ("strong" scaling); the collectives are inside the step.
+          all-gather bf16 params.  Total work is fixed at every N, 1 included ("strong" scaling); the collectives
+          are inside the step.
+  configs (N = 1 only) C1-C4 of BASELINE.json -- 1M-param Adam, GPT-2-small amp step (3-pass and fused, overflow
+          variant), 50 000-tensor SGD / scale, BERT-large LAMB -- timed after the headline with the same event method
+          (bench_configs.py) and reported under "configs" with ms / gbs / frac / reference_cuda_ms / clocks.
 
 `value`   params/s with everything resident in HBM (CUDA events over K back-to-back steps, max over ranks).
 `e2e`     params/s through the same public call with the step's input (the gradients) arriving from pinned HOST
@@ -166,7 +170,7 @@ def run_reference_arm(args, rank, world):
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-        "scaling": "strong" if args.gpus > 1 else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "llama3_8b mixed-precision AdamW (bf16 g, fp32 p/m/v, bf16 copy), CPU slice",
                    "params_in_sample": sample},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
@@ -239,6 +243,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-refcuda", action="store_true", help="skip timing the reference's CUDA kernels (oracle/_ref)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1-C4 side table (bench_configs.py)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -323,7 +328,7 @@ def main():
                            f"{traffic['captured_workload']} ({traffic['source']}), scaled to this launch")
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"{args.workload}: mixed-precision AdamW, bf16 grads + fp32 p/m/v + bf16 model copy "
                                f"({len(numels)} tensors, {P} params), one amp_C.multi_tensor_fused_adam call per step",
@@ -353,11 +358,23 @@ def main():
         except Exception as e:  # noqa: BLE001
             log("[bench] e2e leg failed:", repr(e))
             line["e2e"] = {"value": None, "unit": UNIT, "error": repr(e)[:200]}
+
+    # ---- C1-C4 (BASELINE.json's other configs), same event method, own clock window each -------------------------
+    del step, lists, hp, g, pc, p, m, v      # hand the 128 GB back first
+    torch.cuda.empty_cache()
+    if not args.no_configs:
+        try:
+            from bench_configs import run_configs
+
+            line["configs"] = run_configs(amp_C, device, max(10, args.steps), args.warmup, peak, sampler,
+                                          ClockSampler.summarize, log, with_ref=not args.no_refcuda)
+        except Exception as e:  # noqa: BLE001
+            log("[bench] configs leg failed:", repr(e))
+            line["configs"] = {"error": repr(e)[:300]}
     sampler.stop()
 
     # ---- CPU baseline ------------------------------------------------------------------------------------------------
     if not args.no_cpu:
-        del lists
         sample = int(os.environ.get("MT_BENCH_CPU_SAMPLE", 256 * 1024 * 1024))
         r = cpu_arm(sample, budget_s=20.0)
         line["cpu_baseline"] = {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -39,7 +39,8 @@ enum {
     MT_OK = 0,
     MT_EINVAL = -1,   /* bad argument (depth, dtype combination, null pointer, size mismatch) */
     MT_ECUDA = -2,    /* a CUDA runtime call failed (message has the cudaError string) */
-    MT_ECAPTURE = -3, /* device-table cache miss while the stream is being captured: run one eager warm-up call first */
+    MT_ECAPTURE = -3, /* not possible on a capturing stream: a device-table cache miss (run one eager warm-up call first),
+                         or an entry point that cannot be recorded at all (mt_multi_tensor_l2norm_noalloc) */
     MT_ESCRATCH = -4  /* scratch buffer missing or too small */
 };
 
@@ -246,17 +247,21 @@ int mt_multi_tensor_fused_adam_p2p(int chunk_size, int32_t* noop_flag, const MtT
  *
  * Same result as mt_multi_tensor_l2norm (same kernels, same summation order), but it takes no scratch pointer and makes
  * no cudaMalloc / cudaFree / cudaMallocHost call of its own: the tensor table and the per-chunk partial sums live in a
- * fixed __device__ array inside the library, mt_noalloc_resident_bytes() bytes (about 1.3 MB) on every GPU that loads it.
+ * fixed __device__ array inside the library, mt_noalloc_resident_bytes() bytes (about 1.4 MB) on every GPU that loads it.
  * Meant for hosts bound to the bare C ABI that own no device allocator, for processes that gave all of HBM to one pool
  * at start-up (cudaMalloc would fail), and for steps that must not incur cudaMalloc's device-wide synchronisation.
  *
  * Limits: at most MT_NOALLOC_MAX_TENSORS tensors and MT_NOALLOC_MAX_CHUNKS chunks (sum over tensors of
  * ceil(numel / chunk_size)); beyond either the call returns MT_EINVAL with a message and launches nothing.
- * The array is shared by all calls in the process and is never cleared (nothing in it needs to start at zero: a call
- * reads only what it has itself just written).  Calls whose GPU work overlaps -- different streams or threads -- race
+ * The array is shared by all calls in the process and keeps the previous call's contents; a call reads back only
+ * what it has itself just written, and clears the one part that has to start at zero (its per-tensor completion
+ * counters) with a cudaMemsetAsync on `stream` first.  Calls whose GPU work overlaps -- different streams or threads -- race
  * on it; calls on one stream are safe.  The first call on each device resolves the array's address
  * (cudaGetSymbolAddress): issue it before any stream capture begins.  The table is uploaded from pageable host
- * memory, so the call may wait for earlier work on `stream`. */
+ * memory, so the call may wait for earlier work on `stream`.
+ * Never call it on a stream that is being captured -- not the first call, not a later one: the table is staged through
+ * one host buffer shared by all calls, so a graph replay would upload whatever the most recent call left there.  A
+ * capturing stream is refused with MT_ECAPTURE and nothing is enqueued (the capture itself stays valid). */
 #define MT_NOALLOC_MAX_TENSORS 16384
 #define MT_NOALLOC_MAX_CHUNKS 262144
 int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,
@@ -267,6 +272,8 @@ size_t mt_noalloc_resident_bytes(void);
  * /root/reference/csrc/multi_tensor_apply.cuh:19-26). */
 typedef struct MtCacheStats {
     uint64_t hits, misses, uploads_bytes, entries, device_bytes;
+    uint64_t evictions;          /* entries dropped by the LRU (only idle ones: their events had completed) */
+    uint64_t cross_stream_waits; /* hits that had to order a stream behind another stream's upload / last use */
 } MtCacheStats;
 int mt_table_cache_stats(int device, MtCacheStats* out);
 int mt_table_cache_clear(int device);

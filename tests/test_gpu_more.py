@@ -138,8 +138,12 @@ def test_l2norm_mp(amp_C, oracle):
     # flag already set: the kernels return at once and the outputs are left untouched
     f.fill_(1)
     launches = amp_C.launch_count()
-    n3, _ = amp_C.multi_tensor_l2norm_mp(65536, f, [xs], False)
-    assert amp_C.launch_count() - launches == 2 and f.item() == 1
+    n3, pt3 = amp_C.multi_tensor_l2norm_mp(65536, f, [xs], True)
+    assert amp_C.launch_count() - launches == 1 and f.item() == 1      # one launch: the finalize rides in it
+    # ... and the completion counters were handed back at zero: the next call on the same lists is right again
+    f.zero_()
+    n4, pt4 = amp_C.multi_tensor_l2norm_mp(65536, f, [xs], True)
+    assert bits_equal(n4, n2) and bits_equal(pt4, pt2) and f.item() == 0
 
 
 @pytest.mark.parametrize("g_t,masters", [(F32, False), (F16, False), (F16, True), (BF16, True)])

@@ -79,3 +79,56 @@ def test_noalloc_l2norm_refuses_sizes_beyond_its_built_in_limits():
     rc = L.mt_multi_tensor_l2norm_noalloc(65536, _lib.vp(f), tl.ref, 0, _lib.vp(r), None, _lib.stream_ptr())
     assert rc == -1 and b"MT_NOALLOC_MAX_TENSORS" in L.mt_last_error()
     assert L.mt_launch_count() == launches  # nothing was launched
+
+
+def test_noalloc_l2norm_allocates_nothing_and_refuses_a_capturing_stream():
+    """Backs two statements of the header: the entry point makes no device allocation of its own (free memory as seen
+    by the driver is the same before and after a series of calls, also for list shapes it has not met before), and a
+    stream that is being captured is turned away with MT_ECAPTURE -- without spoiling the capture -- because the
+    table is staged through one host buffer that every later call overwrites."""
+    from beforeholiday_b200 import _lib
+
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(11)
+    sets = [[torch.randn(n, generator=g).cuda() for n in ns] for ns in ((5000, 3), (70001,), (1, 2, 3, 4, 100000))]
+    f = torch.zeros(1, dtype=torch.int32, device="cuda")
+    r = torch.zeros(1, device="cuda")
+    pts = [torch.zeros(len(xs), device="cuda") for xs in sets]
+    tls = [_lib.Lists([xs]) for xs in sets]
+    _lib.check(L.mt_multi_tensor_l2norm_noalloc(4096, _lib.vp(f), tls[0].ref, 1, _lib.vp(r), _lib.vp(pts[0]),
+                                                _lib.stream_ptr()))  # first call on the device: address lookup
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for _ in range(3):
+        for tl, pt, xs in zip(tls, pts, sets):
+            _lib.check(L.mt_multi_tensor_l2norm_noalloc(4096, _lib.vp(f), tl.ref, 1, _lib.vp(r), _lib.vp(pt),
+                                                        _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, "the no-alloc entry point changed the device's free memory"
+    for pt, xs in zip(pts, sets):
+        exact = torch.stack([t.double().norm() for t in xs]).float()
+        assert torch.allclose(pt, exact, rtol=1e-5, atol=0)
+
+    # on a capturing stream: refused, nothing enqueued, the capture survives and replays what WAS recorded
+    y = torch.zeros(4, device="cuda")
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    launches = L.mt_launch_count()
+    with torch.cuda.stream(s):
+        graph.capture_begin()
+        y.add_(1.0)
+        rc = L.mt_multi_tensor_l2norm_noalloc(4096, _lib.vp(f), tls[1].ref, 1, _lib.vp(r), _lib.vp(pts[1]),
+                                              C.c_void_p(s.cuda_stream))
+        graph.capture_end()
+    assert rc == -3 and b"captured" in L.mt_last_error()
+    assert L.mt_launch_count() == launches
+    graph.replay()
+    torch.cuda.synchronize()
+    assert float(y[0]) == 1.0
+    # a different call afterwards, eagerly, still works
+    _lib.check(L.mt_multi_tensor_l2norm_noalloc(4096, _lib.vp(f), tls[2].ref, 1, _lib.vp(r), _lib.vp(pts[2]),
+                                                _lib.stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.allclose(pts[2], torch.stack([t.double().norm() for t in sets[2]]).float(), rtol=1e-5, atol=0)
