@@ -109,7 +109,7 @@ extern "C" int mt_multi_tensor_novograd(int chunk_size, int32_t* noop_flag, cons
             rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tn, prm, noop_flag, tl->device, stream);
         } else {
             using Op = L2NormOp<Tx, false>;
-            typename Op::Params prm{partials};
+            typename Op::Params prm{NormOut{partials, nullptr, nullptr, 1}};
             rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tn, prm, noop_flag, tl->device, stream);
         }
     })

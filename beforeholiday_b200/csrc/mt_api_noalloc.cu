@@ -145,7 +145,7 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
         constexpr int U = sizeof(Tx) == 4 ? 2 : 4;
         using Op = L2NormOp<Tx, false>;
-        typename Op::Params prm{NormOut{partials, ret, ret_pt}};
+        typename Op::Params prm{NormOut{partials, ret, ret_pt, 1}};
         rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
     })
     return rc;

@@ -66,6 +66,14 @@ int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, f
     return MT_OK;
 }
 
+// A large chunk_size (FusedLAMB passes 65536) gives too few CTAs for an even last wave: GPT-2's 124 M gradients are
+// 1 950 chunks = 3.3 waves of 148 SMs x 4 CTAs, and the fourth, one-third-full wave cost 20 % of the pass.  Such chunks
+// are therefore walked as several tiles of 8192 elements; the flag keeps its per-chunk meaning (NormOut::sub).
+int norm_tiles_per_chunk(int chunk_size) {
+    constexpr int kTile = 8192;
+    return (chunk_size > kTile && chunk_size % kTile == 0) ? chunk_size / kTile : 1;
+}
+
 static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int depth,
                        bool mp, float scale, int per_tensor, float* ret, float* ret_per_tensor, void* scratch,
                        size_t scratch_bytes, cudaStream_t stream) {
@@ -77,7 +85,8 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     DeviceGuard guard(tl->device);
     if (!guard.ok) return set_error(MT_ECUDA, "%s: cannot select CUDA device %d", who, tl->device);
     TableRef tb;
-    rc = get_table(tl, chunk_size, stream, &tb);
+    const int sub = norm_tiles_per_chunk(chunk_size);
+    rc = get_table(tl, chunk_size / sub, stream, &tb);
     if (rc) return rc;
     const size_t need = (size_t)tb.ntiles * sizeof(float);
     if (need > 0 && (!scratch || scratch_bytes < need))
@@ -86,7 +95,7 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     float* ret_pt = per_tensor ? ret_per_tensor : nullptr;
     if (tb.ntiles == 0)  // every tensor empty: zeros, by the small kernel (no tile exists to do it in-launch)
         return launch_norm_finalize(tb, partials, 1, ret, ret_pt, tl->device, stream, mp ? noop_flag : nullptr);
-    const NormOut out{partials, ret, ret_pt};
+    const NormOut out{partials, ret, ret_pt, sub};
     // Bytes in flight per thread: 2 groups of 32 B for fp32, 4 groups of 16 B for the 16-bit types (a pure reduction
     // has registers to spare, and 16-byte loads need twice the depth to cover the same latency).
     constexpr int G = 8, THREADS = 256, MINB = 4;
@@ -118,7 +127,7 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
 
 extern "C" size_t mt_norm_scratch_bytes(int chunk_size, const MtTensorLists* tl) {
     if (!tl || !tl->numel || chunk_size <= 0) return 0;
-    return (size_t)mt::count_tiles(tl, chunk_size) * sizeof(float);
+    return (size_t)mt::count_tiles(tl, chunk_size / mt::norm_tiles_per_chunk(chunk_size)) * sizeof(float);
 }
 
 extern "C" int mt_multi_tensor_l2norm(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int per_tensor,

@@ -18,16 +18,21 @@ static void bias_corrections(float beta1, float beta2, int step, int bias_correc
     }
 }
 
-// LAMB stage 1 keeps two norm accumulators live across the IEEE-division helper calls: under the 64-register cap of
-// 4 CTAs/SM ptxas spills them inside the element loop, at 80 registers (3 CTAs/SM) it does not
-// (profiles/r2_sass_summary.txt).  MT_LAMB_STAGE1_MINB=4 selects the old build for A/B timing.
-static bool lamb_stage1_wide() {
-    static const bool wide = [] {
+// LAMB stage 1 keeps two norm accumulators live across the tile's rounds: under the 64-register cap of 4 CTAs/SM ptxas
+// spills a few values (LDL/STL at round boundaries; profiles/r2_sass_summary.txt), at 80 registers (3 CTAs/SM) it does
+// not.  Measured on BERT-large (profiles/r2_lamb_minb_ab.jsonl): multi_tensor_lamb 2.249 ms at 4 CTAs/SM vs 2.295 ms
+// at 3 -- occupancy is worth more than the spills, so 4 stays the default for it.  MT_LAMB_STAGE1_MINB=3|4 forces
+// either build of both stage-1 kernels for A/B timing.
+static int lamb_minb_override() {
+    static const int v = [] {
         const char* e = getenv("MT_LAMB_STAGE1_MINB");
-        return !(e && atoi(e) == 4);
+        const int x = e ? atoi(e) : 0;
+        return (x == 3 || x == 4) ? x : 0;
     }();
-    return wide;
+    return v;
 }
+static bool lamb_stage1_wide() { return lamb_minb_override() == 3; }
+static bool lamb_mp_stage1_wide() { return lamb_minb_override() != 4; }
 
 static inline size_t align256(size_t x) { return (x + 255) / 256 * 256; }
 
@@ -223,13 +228,13 @@ extern "C" int mt_multi_tensor_lamb(int chunk_size, int32_t* noop_flag, const Mt
         if (mode == 0) {
             using Op1 = LambStage1Op<Tp, 0>;
             typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
-                                    global_grad_norm, NormOut{partials, nullptr, pnorm}, mode, need_norms};
+                                    global_grad_norm, NormOut{partials, nullptr, pnorm, 1}, mode, need_norms};
             rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream)
                                     : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
         } else {
             using Op1 = LambStage1Op<Tp, 1>;
             typename Op1::Params p1{beta1, beta2, beta3, bc1, bc2, epsilon, weight_decay, max_grad_norm,
-                                    global_grad_norm, NormOut{partials, nullptr, pnorm}, mode, need_norms};
+                                    global_grad_norm, NormOut{partials, nullptr, pnorm, 1}, mode, need_norms};
             rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream)
                                     : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream);
         }
@@ -277,14 +282,14 @@ extern "C" int mt_multi_tensor_lamb_mp(int chunk_size, int32_t* noop_flag, const
         if (mode == 0) {                                                                                            \
             using Op1 = LambMpStage1Op<TG, TP, 0>;                                                                  \
             typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
-                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm}, mode, bias_correction, need_norms}; \
-            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
+                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm, 1}, mode, bias_correction, need_norms}; \
+            rc = lamb_mp_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
                                     : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream); \
         } else {                                                                                                    \
             using Op1 = LambMpStage1Op<TG, TP, 1>;                                                                  \
             typename Op1::Params p1{beta1, beta2, beta3, epsilon, weight_decay, step, global_grad_norm,             \
-                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm}, mode, bias_correction, need_norms}; \
-            rc = lamb_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
+                                    max_grad_norm, inv_scale, NormOut{partials, nullptr, pnorm, 1}, mode, bias_correction, need_norms}; \
+            rc = lamb_mp_stage1_wide() ? launch_table_kernel<Op1, kG, kU, kThreads, 3>(tb, p1, noop_flag, tl->device, stream) \
                                     : launch_table_kernel<Op1, kG, kU, kThreads, kMinBlocks>(tb, p1, noop_flag, tl->device, stream); \
         }                                                                                                           \
         if (rc) return rc;                                                                                          \

@@ -271,24 +271,30 @@ struct NormOut {
     float* partials;    // [NSETS][ntiles] scratch
     float* ret_global;  // [NSETS] or NULL
     float* ret_pt;      // [NSETS][ntensors] or NULL
+    // Tiles per reference chunk (1 unless the l2norm entry points split a large chunk_size into several tiles to get
+    // enough CTAs for an even last wave).  The overflow flag keeps the reference's per-CHUNK meaning
+    // (csrc/multi_tensor_l2norm_kernel.cu:103-104: "this chunk's sum of squares is not finite"): the tensor's
+    // finalizer rebuilds every chunk's sum from its `sub` consecutive tile partials and tests that.
+    int sub;
 };
 
 template <int THREADS> constexpr int kSmemFloats = 512 / 32 + 4;
 
 template <int THREADS, int NSETS, bool kQuietWhenFlagged>
 __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t, uint32_t tile, const NormOut& o,
-                                               float* smem, const int32_t* noop) {
+                                               float* smem, int32_t* noop) {
     static_assert(THREADS == 256, "the global reduction emulates a 512-thread block with two accumulators per thread");
     unsigned* sflag = reinterpret_cast<unsigned*>(smem + 512 / 32);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool per_tensor = o.ret_pt != nullptr || o.sub > 1;
     if (tid == 0) {
         unsigned r = 0;
         __threadfence();  // this tile's partials (and flag) before its tickets
-        if (o.ret_pt) {
+        if (per_tensor) {
             const uint32_t b = __ldg(tb.tile_begin + t.tensor), e = __ldg(tb.tile_begin + t.tensor + 1);
             if (atomicAdd(tb.tickets + t.tensor, 1u) + 1u == e - b) r |= 1u;
             const bool quiet = kQuietWhenFlagged && *reinterpret_cast<const volatile int32_t*>(noop) != 0;
-            if (!quiet) {
+            if (o.ret_pt && !quiet) {
                 if (t.start == 0)
                     for (int k = t.tensor - 1; k >= 0 && __ldg(tb.tile_begin + k) == b; k--)
                         for (int s = 0; s < NSETS; s++) o.ret_pt[(size_t)s * tb.ntensors + k] = 0.f;
@@ -309,15 +315,24 @@ __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t
     const bool quiet = kQuietWhenFlagged && *reinterpret_cast<const volatile int32_t*>(noop) != 0;
     if ((r & 1u) && warp == 0) {
         const uint32_t b = __ldg(tb.tile_begin + t.tensor), e = __ldg(tb.tile_begin + t.tensor + 1);
+        const uint32_t sub = (uint32_t)o.sub, nchunks = (e - b + sub - 1) / sub;
+        bool bad = false;
 #pragma unroll
         for (int s = 0; s < NSETS; s++) {
             const float* p = o.partials + (size_t)s * tb.ntiles;
             float acc = 0.f;
-            for (uint32_t i = b + lane; i < e; i += 32) acc = fadd(acc, __ldcg(p + i));
+            for (uint32_t c = lane; c < nchunks; c += 32) {
+                const uint32_t i0 = b + c * sub, i1 = min(i0 + sub, e);
+                float cs = __ldcg(p + i0);
+                for (uint32_t i = i0 + 1; i < i1; i++) cs = fadd(cs, __ldcg(p + i));
+                bad = bad || !finite_f(cs);
+                acc = fadd(acc, cs);
+            }
 #pragma unroll
             for (int k = 16; k > 0; k >>= 1) acc = fadd(acc, __shfl_xor_sync(0xffffffffu, acc, k));
-            if (lane == 0 && !quiet) o.ret_pt[(size_t)s * tb.ntensors + t.tensor] = fsqrt(acc);
+            if (lane == 0 && o.ret_pt && !quiet) o.ret_pt[(size_t)s * tb.ntensors + t.tensor] = fsqrt(acc);
         }
+        if (sub > 1 && __any_sync(0xffffffffu, bad) && lane == 0) *noop = 1;
         if (lane == 0) tb.tickets[t.tensor] = 0u;
     }
     if (r & 2u) {

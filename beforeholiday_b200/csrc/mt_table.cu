@@ -129,6 +129,15 @@ namespace {
 
 constexpr int kUseSlots = 4;
 
+// Event queries / waits and pinned allocations are "potentially unsafe" calls: while a stream capture in global mode is
+// open (on this thread or any other) the runtime refuses them AND invalidates the capture.  None of the calls made
+// here touches captured work, so the cache's slow paths run with this thread's capture-interaction mode relaxed.
+struct RelaxedCaptureMode {
+    cudaStreamCaptureMode mode = cudaStreamCaptureModeRelaxed;
+    RelaxedCaptureMode() { cudaThreadExchangeStreamCaptureMode(&mode); }
+    ~RelaxedCaptureMode() { cudaThreadExchangeStreamCaptureMode(&mode); }
+};
+
 struct Entry {
     std::vector<uint8_t> host;  // exact blob, for collision-proof comparison
     void* dev = nullptr;
@@ -287,6 +296,7 @@ int acquire_locked(DeviceCache& c, Entry* e, cudaStream_t stream, bool capturing
     e->tick = ++c.clock;
     *slot_out = -1;
     if (!e->upload_done) {
+        RelaxedCaptureMode relaxed;
         if (cudaEventQuery(e->upload_ev) == cudaSuccess) {
             e->upload_done = true;
         } else {
@@ -310,6 +320,7 @@ int acquire_locked(DeviceCache& c, Entry* e, cudaStream_t stream, bool capturing
     for (int i = 0; i < kUseSlots && slot < 0; i++)
         if (!e->use_ev[i]) slot = i;
     if (slot < 0) {  // every slot belongs to another stream: take one over, inheriting what it guards
+        RelaxedCaptureMode relaxed;
         for (int k = 0; k < kUseSlots && slot < 0; k++) {
             const int i = (e->use_next + k) % kUseSlots;
             if (!e->use_live[i] || cudaEventQuery(e->use_ev[i]) == cudaSuccess) { e->use_live[i] = false; slot = i; }
@@ -428,6 +439,7 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, Tabl
     const uint64_t h = hash_blob(blob.data(), bytes);
 
     std::lock_guard<std::mutex> lk(c.mu);
+    RelaxedCaptureMode relaxed;  // miss path: eviction queries, staging waits, pinned allocation
     Entry* e = nullptr;
     auto range = c.map.equal_range(h);
     for (auto it = range.first; it != range.second; ++it)

@@ -43,7 +43,7 @@ class _Timer:
         self.flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)
         self.sampler, self.summarize = sampler, summarize
 
-    def __call__(self, fn, min_wall_s=0.4, max_rounds=40):
+    def __call__(self, fn, min_wall_s=0.45, max_rounds=100000):
         """-> (gpu ms per step, host enqueue ms per step, clocks record)."""
         for _ in range(self.warmup):
             fn()

@@ -194,6 +194,20 @@ def main():
             report("C4 BERT-large 336M", "LAMB step incl. grad norm", name, ms, host, (44 if mod is mine else 52) * P, P,
                    launches_of(lamb_step) if mod is mine else None,
                    {"bytes_per_param": 44 if mod is mine else 52})
+        # mixed-precision LAMB (fp16 grads + model copy, fp32 masters): the "_mp" kernels
+        g16 = [t.half() for t in g]
+        p16 = [t.half() for t in p]
+        dv = lambda val, dt=torch.float32: torch.tensor([val], dtype=dt, device="cuda")
+        lr_d, step_d, mx_d, inv_d, fi_d = dv(5e-4), dv(3, torch.int32), dv(1.0), dv(1.0), dv(0.0)
+        def lamb_mp_step():
+            gn, _ = mine.multi_tensor_l2norm_mp(65536, flag, [g16], False)
+            mine.multi_tensor_lamb_mp(8192, flag, [g16, p, m, v, p16], lr_d, 0.9, 0.999, 1e-6, step_d, 1, 0.01, 1, 1, gn, mx_d,
+                                      False, fi_d, inv_d)
+        flag.zero_()
+        ms, host = timeit(lamb_mp_step, args.iters)
+        report("C4 BERT-large 336M", "LAMB-mp step incl. grad norm (fp16 g + copy, fp32 p/m/v)", "b200", ms, host, 38 * P, P,
+               launches_of(lamb_mp_step), {"bytes_per_param": 38, "flag": int(flag.item())})
+        del g16, p16
         # the CPU step beside it (north star): the oracle's LAMB restatement (OpenMP, all host cores) on the same set
         try:
             import os
