@@ -7,6 +7,8 @@
 // (no float atomics); replaces cleanup / cleanup_v3 (csrc/multi_tensor_l2norm_kernel.cu:198-237), which are separate
 // launches in the reference.  norm_finalize_kernel is what remains of this library's own second launch: it serves the
 // degenerate all-tensors-empty call only.
+#include <cstdlib>
+
 #include "mt_host.h"
 #include "mt_ops.cuh"
 
@@ -66,12 +68,18 @@ int launch_norm_finalize(const DevTable& tb, const float* partials, int nsets, f
     return MT_OK;
 }
 
-// A large chunk_size (FusedLAMB passes 65536) gives too few CTAs for an even last wave: GPT-2's 124 M gradients are
-// 1 950 chunks = 3.3 waves of 148 SMs x 4 CTAs, and the fourth, one-third-full wave cost 20 % of the pass.  Such chunks
-// are therefore walked as several tiles of 8192 elements; the flag keeps its per-chunk meaning (NormOut::sub).
+// One tile per reference chunk by default.  Splitting a large chunk_size (FusedLAMB passes 65536) into several tiles
+// gives the last wave more CTAs to balance with, but every tile pays a fence + two atomics + a barrier for its
+// completion tickets: measured on GPT-2's 124 M fp16 gradients (profiles/r2_norm_tile_sweep.jsonl) 8192-element tiles
+// took 118 us against 55 us for whole chunks.  MT_NORM_TILE=<elements> (a divisor of chunk_size) overrides, for sweeps;
+// the flag keeps its per-chunk meaning either way (NormOut::sub).
 int norm_tiles_per_chunk(int chunk_size) {
-    constexpr int kTile = 8192;
-    return (chunk_size > kTile && chunk_size % kTile == 0) ? chunk_size / kTile : 1;
+    static const int forced = [] {
+        const char* e = getenv("MT_NORM_TILE");
+        return e ? atoi(e) : 0;
+    }();
+    if (forced > 0 && chunk_size > forced && chunk_size % forced == 0) return chunk_size / forced;
+    return 1;
 }
 
 static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, const MtTensorLists* tl, int depth,

@@ -223,10 +223,21 @@ struct Tile {
 __device__ __forceinline__ Tile locate_tile(const DevTable& tb, uint32_t tile) {
     // upper_bound(tile_begin, tile) - 1 : last tensor whose first tile is <= tile.  Empty tensors have
     // tile_begin[t] == tile_begin[t+1] and are skipped naturally.
+    // 33-ary search: the 32 lanes of a warp each probe one point of [lo, hi) and vote, so 291 tensors take 2 dependent
+    // loads and 50 000 take 4 (a bisection: 9 and 16).  That latency sits at the head of every CTA; it is hidden while
+    // other CTAs of the SM stream, but not at the start of a launch, which is what a 40-microsecond norm pass feels.
+    // Called with the whole CTA converged (the tile index is uniform), every warp searching redundantly.
     int lo = 0, hi = tb.ntensors;  // invariant: tile_begin[lo] <= tile < tile_begin[hi]
+    const int lane = threadIdx.x & 31;
     while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (__ldg(tb.tile_begin + mid) <= tile) lo = mid; else hi = mid;
+        const int span = hi - lo;
+        const int probe = lo + (int)(((long long)span * (lane + 1)) / 33);
+        const unsigned le = __ballot_sync(0xffffffffu, __ldg(tb.tile_begin + probe) <= tile);
+        const int k = __popc(le);  // probes are non-decreasing and tile_begin is sorted: the true votes form a prefix
+        const int nlo = k > 0 ? lo + (int)(((long long)span * k) / 33) : lo;
+        const int nhi = k < 32 ? lo + (int)(((long long)span * (k + 1)) / 33) : hi;
+        lo = nlo;
+        hi = nhi > lo ? nhi : lo + 1;
     }
     Tile t;
     t.tensor = lo;

@@ -244,7 +244,7 @@ def test_c_abi_direct_ctypes(oracle):
     xs = [rnd(300001, F32, 20), rnd(5, F32, 21)]
     tl = _lib.Lists([xs])
     nbytes = L.mt_norm_scratch_bytes(65536, tl.ref)
-    assert nbytes == 4 * (37 + 1)          # chunks of 65536 are walked as 8 tiles of 8192: one partial per tile
+    assert nbytes == 4 * (5 + 1)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
     ret, ret_pt = torch.empty(1, device="cuda"), torch.empty(2, device="cuda")
     _lib.check(L.mt_multi_tensor_l2norm(65536, _lib.vp(f), tl.ref, 1, _lib.vp(ret), _lib.vp(ret_pt), _lib.vp(scratch),
