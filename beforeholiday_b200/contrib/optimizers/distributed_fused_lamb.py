@@ -32,7 +32,7 @@ from typing import List, Optional
 import torch
 import torch.distributed as dist
 
-from .distributed_fused_adam import FlatLayout
+from .flat_sharded_adam import FlatLayout
 
 
 class DistributedFusedLAMB(torch.optim.Optimizer):
