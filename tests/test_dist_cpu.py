@@ -10,7 +10,12 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam, FlatLayout
+import sys
+
+from beforeholiday_b200.contrib.optimizers import FlatLayout
+
+sys.path.insert(0, os.path.dirname(__file__))
+from cpu_engine import CpuDistributedFusedAdam, CpuShardedAdam  # noqa: E402  (gloo + oracle stand-ins)
 
 SIZES = [1000, 7, 4096, 33333, 1, 129]
 
@@ -38,41 +43,6 @@ def test_layout_partitions_flat_space_exactly():
         assert elems == sum(SIZES)                 # every parameter element lands in exactly one fragment
 
 
-class CpuShardedAdam(DistributedFusedAdam):
-    """gloo + oracle stand-ins for the NCCL collectives and the CUDA update."""
-
-    def _init_comm(self):
-        self.rs_group = self.ag_group = self.group
-        self.rs_stream = self.ag_stream = None
-
-    def _reduce_scatter(self, b):
-        lo, hi = self.layout.bucket_range(b)
-        buf = self.grads_flat[lo:hi].float()
-        dist.all_reduce(buf, group=self.group)
-        olo, ohi = self.layout.owned_range(b)
-        self.grads_flat[olo:ohi].copy_(buf[olo - lo:ohi - lo])  # only the owned sub-shard is defined afterwards
-
-    def _all_gather(self, b):
-        lo, hi = self.layout.bucket_range(b)
-        olo, ohi = self.layout.owned_range(b)
-        parts = [torch.empty(self.layout.sub_shard, dtype=torch.float32) for _ in range(self.world)]
-        dist.all_gather(parts, self.params_flat[olo:ohi].float().contiguous(), group=self.group)
-        self.params_flat[lo:hi].copy_(torch.cat(parts))
-
-    def _update_bucket(self, b, grad_scale):
-        from oracle import mt_oracle as O
-
-        lists, hp = self._per_bucket[b]
-        if lists[0]:   # grad_scale is a 1-element tensor on the clipped route (device-side divisor in the product)
-            O.multi_tensor_fused_adam(8192, self.noop, lists, *[h.tolist() for h in hp], self.lr, float(grad_scale),
-                                      self.step_count, 1 if self.adam_w_mode else 0, honour_noop=True)
-
-    def grad_norm(self, grads_are_reduced=True):
-        sq = sum((l.double() ** 2).sum() for (lists, _) in self._per_bucket for l in lists[3]).float().reshape(1)
-        dist.all_reduce(sq, group=self.group)
-        return sq.sqrt()
-
-
 def _worker(rank, world, port, outdir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -80,7 +50,7 @@ def _worker(rank, world, port, outdir):
         torch.manual_seed(0)
         full = [torch.randn(n) * 0.02 for n in SIZES]
         wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
-        opt = CpuShardedAdam(numels=SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0, device="cpu",
+        opt = CpuShardedAdam(SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.0, device="cpu",
                              grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16, bucket_cap_mb=8192 * 2 / 2 ** 20,
                              per_param_weight_decay=wds)
         L = opt.layout
@@ -290,8 +260,8 @@ def _module_cpu_worker(rank, world, port, outdir, clip=False):
         ref.load_state_dict(model.state_dict())
         decay = [p for n, p in model.named_parameters() if n.endswith("weight")]
         no_decay = [p for n, p in model.named_parameters() if n.endswith("bias")]
-        opt = CpuShardedAdam([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
-                             lr=1e-2, betas=(0.9, 0.95), eps=1e-8, bucket_cap_mb=71 * 4 / 2 ** 20)
+        opt = CpuDistributedFusedAdam([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
+                                      lr=1e-2, betas=(0.9, 0.95), eps=1e-8, bucket_cap_mb=71 * 4 / 2 ** 20, device="cpu")
         assert opt.layout.nbuckets > 1 and opt.grads_flat.dtype == torch.float32
         assert all(p.data_ptr() == opt.params_flat.data_ptr() + 4 * o for p, o in zip(decay + no_decay, opt.layout.offsets))
         rdecay = [p for n, p in ref.named_parameters() if n.endswith("weight")]
@@ -312,7 +282,8 @@ def _module_cpu_worker(rank, world, port, outdir, clip=False):
                 p.grad /= world
             if clip:
                 rn = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.05)
-                n = opt.step(max_grad_norm=0.05)
+                n = opt.clip_grad_norm(0.05)
+                opt.step()
                 assert abs(float(n) - float(rn)) <= 1e-5 * float(rn) and float(rn) > 0.05   # it really clips
             else:
                 opt.step()
