@@ -19,11 +19,11 @@ def _worker(rank, world, port, outdir, fused=False):
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+        from beforeholiday_b200.contrib.optimizers import FlatShardedAdam
 
         wds = [0.1 if i % 2 else 0.0 for i in range(len(SIZES))]
-        opt = DistributedFusedAdam(numels=SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, device=f"cuda:{rank}",
-                                   bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds, fused_p2p=bool(fused))
+        opt = FlatShardedAdam(SIZES, lr=1e-2, betas=(0.9, 0.95), eps=1e-8, device=f"cuda:{rank}",
+                              bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds, fused_p2p=bool(fused))
         if fused == "mc" and not opt.has_multicast:
             torch.save({"skip": "no NVSwitch multicast on this box"}, os.path.join(outdir, f"rank{rank}.pt"))
             return
@@ -176,6 +176,7 @@ def _module_worker(rank, world, port, outdir, clip):
         opt = DistributedFusedAdam([{"params": decay, "weight_decay": 0.1}, {"params": no_decay, "weight_decay": 0.0}],
                                    lr=1e-2, betas=(0.9, 0.95), eps=1e-8, bucket_cap_mb=71 * 4 / 2 ** 20)
         assert opt.layout.nbuckets > 1 and opt.grads_flat.dtype == torch.float32
+        assert isinstance(opt, torch.optim.Optimizer) and len(opt.param_groups) == 2
         rdecay = [p for n, p in ref.named_parameters() if n.endswith("weight")]
         rno = [p for n, p in ref.named_parameters() if n.endswith("bias")]
         ropt = torch.optim.AdamW([{"params": rdecay, "weight_decay": 0.1}, {"params": rno, "weight_decay": 0.0}],
@@ -193,7 +194,8 @@ def _module_worker(rank, world, port, outdir, clip):
                 p.grad /= world
             if clip:
                 rn = torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
-                n = opt.step(max_grad_norm=0.5)
+                n = opt.clip_grad_norm(0.5)
+                opt.step()
                 norms.append((float(n), float(rn)))
             else:
                 opt.step()
