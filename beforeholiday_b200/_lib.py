@@ -19,7 +19,7 @@ EXPORTS = [
     "mt_multi_tensor_sgd", "mt_multi_tensor_lamb", "mt_multi_tensor_l2norm_mp", "mt_multi_tensor_lamb_mp",
     "mt_multi_tensor_adagrad", "mt_multi_tensor_novograd", "mt_multi_tensor_lars", "mt_multi_tensor_lamb_stage1", "mt_multi_tensor_lamb_stage2",
     "mt_multi_tensor_maybe_cast", "mt_dist_lamb_scratch_bytes", "mt_multi_tensor_lamb_compute_update_term", "mt_multi_tensor_lamb_update_weights",
-    "mt_multi_tensor_fused_adam", "mt_multi_tensor_fused_adam_capturable", "mt_multi_tensor_fused_adam_p2p", "mt_multi_tensor_l2norm_noalloc", "mt_noalloc_resident_bytes",
+    "mt_multi_tensor_fused_adam", "mt_multi_tensor_fused_adam_capturable", "mt_multi_tensor_fused_adam_p2p", "mt_multi_tensor_fused_adam_p2p_hybrid", "mt_multi_tensor_l2norm_noalloc", "mt_noalloc_resident_bytes",
     "mt_table_cache_stats", "mt_table_cache_clear", "mt_launch_count",
 ]
 

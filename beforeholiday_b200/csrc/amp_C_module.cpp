@@ -567,7 +567,8 @@ void multi_tensor_fused_adam_p2p(int chunk_size, at::Tensor noop_flag, TensorLis
                                  at::Tensor per_tensor_bias_correction, at::Tensor per_tensor_eps,
                                  at::Tensor per_tensor_weight_decay, float lr, float grad_scale, int step, int mode,
                                  int rank, std::vector<uint64_t> grad_ptrs, std::vector<uint64_t> param_ptrs,
-                                 uint64_t grad_multicast_ptr, uint64_t param_multicast_ptr) {
+                                 uint64_t grad_multicast_ptr, uint64_t param_multicast_ptr, int ld_p2p_of16,
+                                 int st_p2p_of16) {
     Flat f;
     flatten(tensor_lists, 5, 5, "multi_tensor_fused_adam_p2p", f);
     TORCH_CHECK(grad_ptrs.size() == param_ptrs.size(), "grad_ptrs and param_ptrs must have one entry per rank");
@@ -579,12 +580,12 @@ void multi_tensor_fused_adam_p2p(int chunk_size, at::Tensor noop_flag, TensorLis
         pb[r] = reinterpret_cast<void*>(param_ptrs[r]);
     }
     TORCH_CHECK(per_tensor_bias_correction.scalar_type() == at::ScalarType::Int, "per_tensor_bias_correction must be int32");
-    check(mt_multi_tensor_fused_adam_p2p(chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(),
-                                         per_tensor_beta2.data_ptr<float>(), per_tensor_bias_correction.data_ptr<int32_t>(),
-                                         per_tensor_eps.data_ptr<float>(), per_tensor_weight_decay.data_ptr<float>(), lr,
-                                         grad_scale, step, mode, world, rank, gb.data(), pb.data(),
-                                         reinterpret_cast<const void*>(grad_multicast_ptr),
-                                         reinterpret_cast<void*>(param_multicast_ptr), f.stream));
+    check(mt_multi_tensor_fused_adam_p2p_hybrid(
+        chunk_size, flag_ptr(noop_flag), &f.tl, per_tensor_beta1.data_ptr<float>(), per_tensor_beta2.data_ptr<float>(),
+        per_tensor_bias_correction.data_ptr<int32_t>(), per_tensor_eps.data_ptr<float>(),
+        per_tensor_weight_decay.data_ptr<float>(), lr, grad_scale, step, mode, world, rank, gb.data(), pb.data(),
+        reinterpret_cast<const void*>(grad_multicast_ptr), reinterpret_cast<void*>(param_multicast_ptr), ld_p2p_of16,
+        st_p2p_of16, f.stream));
 }
 
 py::dict table_cache_stats(int device) {
@@ -634,7 +635,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("per_tensor_beta2"), py::arg("per_tensor_bias_correction"), py::arg("per_tensor_eps"),
           py::arg("per_tensor_weight_decay"), py::arg("lr"), py::arg("grad_scale"), py::arg("step"), py::arg("mode"),
           py::arg("rank"), py::arg("grad_ptrs"), py::arg("param_ptrs"), py::arg("grad_multicast_ptr") = 0,
-          py::arg("param_multicast_ptr") = 0);
+          py::arg("param_multicast_ptr") = 0, py::arg("ld_p2p_of16") = 0, py::arg("st_p2p_of16") = 0);
     m.def("maybe_cast_mt", &maybe_cast_mt, "Converting multi-tensor copy, skipped when the overflow flag is set");
     m.def("multi_tensor_lamb_compute_update_term", &multi_tensor_lamb_compute_update_term,
           "Sharded LAMB stage 1: update term (optionally with fused per-parameter norm sums)", py::arg("chunk_size"),

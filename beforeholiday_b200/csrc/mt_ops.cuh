@@ -194,10 +194,17 @@ __device__ __forceinline__ void multimem_st_16B(void* mc, const uint32_t (&w)[4]
                  "r"(w[3]) : "memory");
 }
 
-// kMc = false: peer-to-peer loads / stores on every rank's mapped buffer.
-// kMc = true : the 8-element vector path goes through the multicast address (in-switch reduction and broadcast);
-//              the scalar head / tail elements still use the per-peer pointers.
-template <class Tg, int WORLD, bool kMc> struct DistAdamP2POp : DistAdamOp<Tg, true, true> {
+// kRoute = 0: peer-to-peer loads / stores on every rank's mapped buffer.
+// kRoute = 1: the 8-element vector path goes through the multicast address (in-switch reduction and broadcast);
+//             the scalar head / tail elements still use the per-peer pointers.
+// kRoute = 2: hybrid -- both paths are compiled in and every 32 KB block of the flat buffers picks one, independently
+//             for the gradient loads and the parameter stores: block i (of every 16 consecutive ones) goes peer-to-peer
+//             when i < ld_p2p_of16 / st_p2p_of16, through the switch otherwise.  If the switch's reduction / multicast
+//             path and the plain peer-to-peer path have separate ceilings, a mix moves more bytes per second than
+//             either alone (tools/sweep_p2p.py measures the split).  Both paths deliver the same bits whenever the sum
+//             is exact in Tg (and the same rounding: fp32 accumulate, one rounding to Tg).
+constexpr int kRouteP2P = 0, kRouteMc = 1, kRouteHybrid = 2;
+template <class Tg, int WORLD, int kRoute> struct DistAdamP2POp : DistAdamOp<Tg, true, true> {
     using Base = DistAdamOp<Tg, true, true>;
     static constexpr unsigned kCustomLoad = 0b01000, kCustomStore = 0b10000;
     struct Params {
@@ -206,40 +213,53 @@ template <class Tg, int WORLD, bool kMc> struct DistAdamP2POp : DistAdamOp<Tg, t
         char* pbase[WORLD];        // every rank's flat parameter buffer
         const char* gown;          // = gbase[rank], pbase[rank]: passed separately so that the arrays are only ever
         char* pown;                //   indexed by compile-time constants (a runtime index would spill them to local memory)
-        const char* gmc;           // multicast addresses of the two buffers (kMc only)
+        const char* gmc;           // multicast addresses of the two buffers (kRoute != 0)
         char* pmc;
+        int ld_p2p_of16, st_p2p_of16;  // hybrid split (kRoute == 2)
     };
     Params q;
     __device__ explicit DistAdamP2POp(const Params& prm) : Base(prm.base), q(prm) {}
+    __device__ __forceinline__ static bool block_is_p2p(ptrdiff_t off, int of16) {
+        return (int)(((uint64_t)off >> 15) & 15u) < of16;
+    }
+    template <int G>
+    __device__ __forceinline__ void load_p2p_vec(ptrdiff_t off, float (&x)[G]) const {
+        uint32_t w[WORLD][4];
+#pragma unroll
+        for (int r = 0; r < WORLD; r++) RawVec<4, true>::ld(q.gbase[r] + off, w[r]);  // all peers in flight
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            float lo, hi;
+            Packed16<Tg>::unpack(w[0][i], lo, hi);
+#pragma unroll
+            for (int r = 1; r < WORLD; r++) {
+                float l2, h2;
+                Packed16<Tg>::unpack(w[r][i], l2, h2);
+                lo = fadd(lo, l2);
+                hi = fadd(hi, h2);
+            }
+            x[2 * i] = Elem<Tg>::round(lo);
+            x[2 * i + 1] = Elem<Tg>::round(hi);
+        }
+    }
+    template <int G>
+    __device__ __forceinline__ void load_mc_vec(ptrdiff_t off, float (&x)[G]) const {
+        uint32_t w[4];
+        Multimem<Tg>::ld_reduce(q.gmc + off, w);  // sum over all ranks, fp32 accumulate, rounded once to Tg
+#pragma unroll
+        for (int i = 0; i < 4; i++) Packed16<Tg>::unpack(w[i], x[2 * i], x[2 * i + 1]);
+    }
     template <int D, int G, bool kVec>
     __device__ __forceinline__ void custom_load(const Tg* p, float (&x)[G]) const {
         static_assert(D == 3, "only the gradient list is gathered");
         const ptrdiff_t off = reinterpret_cast<const char*>(p) - q.gown;
         if constexpr (kVec) {
             static_assert(G == 8, "vector path moves 8 x 16-bit = 16 bytes");
-            if constexpr (kMc) {
-                uint32_t w[4];
-                Multimem<Tg>::ld_reduce(q.gmc + off, w);  // sum over all ranks, fp32 accumulate, rounded once to Tg
-#pragma unroll
-                for (int i = 0; i < 4; i++) Packed16<Tg>::unpack(w[i], x[2 * i], x[2 * i + 1]);
-            } else {
-                uint32_t w[WORLD][4];
-#pragma unroll
-                for (int r = 0; r < WORLD; r++) RawVec<4, true>::ld(q.gbase[r] + off, w[r]);  // all peers in flight
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    float lo, hi;
-                    Packed16<Tg>::unpack(w[0][i], lo, hi);
-#pragma unroll
-                    for (int r = 1; r < WORLD; r++) {
-                        float l2, h2;
-                        Packed16<Tg>::unpack(w[r][i], l2, h2);
-                        lo = fadd(lo, l2);
-                        hi = fadd(hi, h2);
-                    }
-                    x[2 * i] = Elem<Tg>::round(lo);
-                    x[2 * i + 1] = Elem<Tg>::round(hi);
-                }
+            if constexpr (kRoute == kRouteMc) load_mc_vec<G>(off, x);
+            else if constexpr (kRoute == kRouteP2P) load_p2p_vec<G>(off, x);
+            else {
+                if (block_is_p2p(off, q.ld_p2p_of16)) load_p2p_vec<G>(off, x);
+                else load_mc_vec<G>(off, x);
             }
         } else {
             float acc = Elem<Tg>::load(reinterpret_cast<const Tg*>(q.gbase[0] + off));
@@ -248,30 +268,38 @@ template <class Tg, int WORLD, bool kMc> struct DistAdamP2POp : DistAdamOp<Tg, t
             x[0] = Elem<Tg>::round(acc);
         }
     }
+    template <int G>
+    __device__ __forceinline__ void store_mc_vec(ptrdiff_t off, const float (&x)[G]) const {
+        uint32_t w[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if constexpr (std::is_same<Tg, __nv_bfloat16>::value) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
+                w[i] = *reinterpret_cast<uint32_t*>(&h);
+            } else {
+                __half2 h = __floats2half2_rn(x[2 * i], x[2 * i + 1]);
+                w[i] = *reinterpret_cast<uint32_t*>(&h);
+            }
+        }
+        multimem_st_16B(q.pmc + off, w);
+    }
     template <int D, int G, bool kVec>
     __device__ __forceinline__ void custom_store(Tg* p, const float (&x)[G]) const {
         static_assert(D == 4, "only the parameter copy is scattered");
         const ptrdiff_t off = reinterpret_cast<const char*>(p) - q.pown;
-        if constexpr (kVec && kMc) {
-            uint32_t w[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                if constexpr (std::is_same<Tg, __nv_bfloat16>::value) {
-                    __nv_bfloat162 h = __floats2bfloat162_rn(x[2 * i], x[2 * i + 1]);
-                    w[i] = *reinterpret_cast<uint32_t*>(&h);
-                } else {
-                    __half2 h = __floats2half2_rn(x[2 * i], x[2 * i + 1]);
-                    w[i] = *reinterpret_cast<uint32_t*>(&h);
-                }
+        if constexpr (kVec && kRoute != kRouteP2P) {
+            bool mc = true;
+            if constexpr (kRoute == kRouteHybrid) mc = !block_is_p2p(off, q.st_p2p_of16);
+            if (mc) {
+                store_mc_vec<G>(off, x);
+                return;
             }
-            multimem_st_16B(q.pmc + off, w);
-        } else {
+        }
 #pragma unroll
-            for (int r = 0; r < WORLD; r++) {
-                Tg* dst = reinterpret_cast<Tg*>(q.pbase[r] + off);
-                if constexpr (kVec) Group<Tg, G, false>::st(dst, x);
-                else Elem<Tg>::store(dst, x[0]);
-            }
+        for (int r = 0; r < WORLD; r++) {
+            Tg* dst = reinterpret_cast<Tg*>(q.pbase[r] + off);
+            if constexpr (kVec) Group<Tg, G, false>::st(dst, x);
+            else Elem<Tg>::store(dst, x[0]);
         }
     }
 };

@@ -242,6 +242,19 @@ int mt_multi_tensor_fused_adam_p2p(int chunk_size, int32_t* noop_flag, const MtT
                                    int world, int rank, const void* const* grad_bases, void* const* param_bases,
                                    const void* grad_multicast, void* param_multicast, void* stream);
 
+/* Same kernel with a per-block choice of route (needs the multicast addresses): of every 16 consecutive 32 KB blocks of
+ * the flat buffers the first ld_p2p_of16 take their gradients by peer-to-peer loads and the first st_p2p_of16 deliver
+ * their parameters by peer-to-peer stores; the other blocks go through the switch (multimem).  0 / 0 is the plain
+ * multicast kernel above, 16 / 16 the plain peer-to-peer one.  Results are bit-identical for every split whenever the
+ * rank sum is exact in the gradient dtype.  Same reference lines as above. */
+int mt_multi_tensor_fused_adam_p2p_hybrid(int chunk_size, int32_t* noop_flag, const MtTensorLists* tl,
+                                          const float* per_tensor_beta1, const float* per_tensor_beta2,
+                                          const int32_t* per_tensor_bias_correction, const float* per_tensor_eps,
+                                          const float* per_tensor_weight_decay, float lr, float grad_scale, int step,
+                                          int mode, int world, int rank, const void* const* grad_bases,
+                                          void* const* param_bases, const void* grad_multicast, void* param_multicast,
+                                          int ld_p2p_of16, int st_p2p_of16, void* stream);
+
 /* L2 norm for callers that cannot allocate.  No counterpart in the reference (its multi_tensor_l2norm_cuda allocates
  * four tensors per call through torch).
  *
