@@ -35,22 +35,108 @@ def _timed(fn, steps, device):
     return float(ms.item()), t0, t1
 
 
+PARITY_SIZES = [1000, 7, 4096, 33333, 1, 129, 300001]
+
+
+def parity_block(amp_C, rank, world, device):
+    """After the timed region: a small sharded run (several buckets, parameter fragments straddling shard boundaries,
+    per-parameter weight decay, 3 steps) through every route, compared ON EVERY RANK bit for bit with the single-GPU
+    kernel (amp_C.multi_tensor_fused_adam) applied to the rank-order sum of the same gradients.  Gradients are small
+    multiples of 2^-10, so every partial sum is exact in bf16 and the order of the reduction cannot matter.  The
+    single-GPU kernel is itself held bit-exact to the CPU oracle by tests/ (bench.py may not execute oracle/ outside
+    its cpu_baseline leg).  Returns {"nccl": bool, "fused_p2p": bool|None, "fused_multicast": bool|None,
+    "fused_hybrid": bool|None, "max_ulp": int}."""
+    from beforeholiday_b200.contrib.optimizers import FlatShardedAdam
+
+    sizes, k = PARITY_SIZES, len(PARITY_SIZES)
+    wds = [0.1 if i % 2 else 0.0 for i in range(k)]
+    hp = dict(lr=1e-2, betas=(0.9, 0.95), eps=1e-8)
+
+    def grads_of(it, r):
+        g = torch.Generator().manual_seed(100 * it + r)
+        return [(torch.randint(-16, 16, (n,), generator=g).float() / 1024) for n in sizes]
+
+    # single-GPU truth
+    torch.manual_seed(0)
+    init = [(torch.randn(n) * 0.02).bfloat16() for n in sizes]
+    p32 = [x.float().to(device) for x in init]
+    m = [torch.zeros(n, device=device) for n in sizes]
+    v = [torch.zeros(n, device=device) for n in sizes]
+    pc = [torch.zeros(n, dtype=torch.bfloat16, device=device) for n in sizes]
+    T = lambda vals, dt: torch.tensor(vals, dtype=dt, device=device)
+    hps = (T([hp["betas"][0]] * k, torch.float32), T([hp["betas"][1]] * k, torch.float32), T([1] * k, torch.int32),
+           T([hp["eps"]] * k, torch.float32), T(wds, torch.float32))
+    flag = torch.zeros(1, dtype=torch.int32, device=device)
+    for it in range(3):
+        tot = [torch.zeros(n) for n in sizes]
+        for r in range(world):
+            for t, g in zip(tot, grads_of(it, r)):
+                t += g
+        gs = [t.bfloat16().to(device) for t in tot]
+        amp_C.multi_tensor_fused_adam(8192, flag, [p32, m, v, gs, pc], *hps, hp["lr"], float(world), it + 1, 1, True)
+    out = {"max_ulp": 0}
+    for route in ("nccl", "fused_p2p", "fused_multicast", "fused_hybrid"):
+        try:
+            opt = FlatShardedAdam(sizes, device=device, bucket_cap_mb=65536 * 2 / 2 ** 20, per_param_weight_decay=wds,
+                                  fused_p2p=(route != "nccl"), **hp)
+            if route != "nccl" and not opt.fused_p2p:
+                out[route] = None
+                continue
+            if route in ("fused_multicast", "fused_hybrid") and not opt.has_multicast:
+                out[route] = None
+                continue
+            L = opt.layout
+            assert L.nbuckets > 1
+            for x, o in zip(init, L.offsets):
+                opt.params_flat[o:o + x.numel()].copy_(x)
+            opt.init_master_from_params()
+            for it in range(3):
+                opt.zero_grad()
+                for g, n, o in zip(grads_of(it, rank), sizes, L.offsets):
+                    opt.grads_flat[o:o + n].copy_(g)
+                if route == "nccl":
+                    opt.step()
+                elif route == "fused_hybrid":
+                    opt.step_fused(multicast=True, ld_p2p_of16=5, st_p2p_of16=9)
+                else:
+                    opt.step_fused(multicast=(route == "fused_multicast"), ld_p2p_of16=0, st_p2p_of16=0)
+            torch.cuda.synchronize(device)
+            worst = 0
+            for want, n, o in zip(pc, sizes, L.offsets):
+                a = opt.params_flat[o:o + n].view(torch.int16).to(torch.int32)
+                b = want.view(torch.int16).to(torch.int32)
+                worst = max(worst, int((a - b).abs().max()))
+            ok = torch.tensor([1 if (worst == 0 and int(opt.noop.item()) == 0) else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            w = torch.tensor([worst], device=device)
+            dist.all_reduce(w, op=dist.ReduceOp.MAX)
+            out[route] = bool(ok.item())
+            out["max_ulp"] = max(out["max_ulp"], int(w.item()))
+            del opt
+        except Exception as e:  # noqa: BLE001
+            out[route] = False
+            out.setdefault("errors", {})[route] = repr(e)[:200]
+    out["vs"] = ("single-GPU amp_C.multi_tensor_fused_adam on the rank-order sum of the gradients, every rank, all "
+                 f"{sum(PARITY_SIZES)} gathered bf16 params, 3 steps, {k} tensors over several buckets")
+    return out
+
+
 def run_distributed(args, rank, world, local_rank, device):
     import beforeholiday_b200
-    from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+    from beforeholiday_b200.contrib.optimizers import FlatShardedAdam
 
     amp_C = beforeholiday_b200.load_amp_C()
     shapes = workloads.WORKLOADS[args.workload]()
     numels = workloads.numels(shapes)
     P = sum(numels)
-    kw = dict(numels=numels, lr=HP["lr"], betas=(HP["beta1"], HP["beta2"]), eps=HP["eps"], weight_decay=HP["wd"],
+    kw = dict(lr=HP["lr"], betas=(HP["beta1"], HP["beta2"]), eps=HP["eps"], weight_decay=HP["wd"],
               adam_w_mode=True, device=device, bucket_cap_mb=1024.0, grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16)
     fused_err = None
     try:  # symmetric-memory buffers: enables the single-kernel reduce-scatter + update + all-gather route
-        opt = DistributedFusedAdam(fused_p2p=True, **kw)
+        opt = FlatShardedAdam(numels, fused_p2p=True, **kw)
     except Exception as e:  # noqa: BLE001
         fused_err = repr(e)[:300]
-        opt = DistributedFusedAdam(fused_p2p=False, **kw)
+        opt = FlatShardedAdam(numels, fused_p2p=False, **kw)
     ok = torch.tensor([1 if opt.fused_p2p else 0], device=device)
     dist.all_reduce(ok, op=dist.ReduceOp.MIN)
     fused = bool(ok.item())
@@ -118,22 +204,51 @@ def run_distributed(args, rank, world, local_rank, device):
         host.copy_(opt.grads_flat[:win])
         host_flag = torch.zeros(1, dtype=torch.int32, pin_memory=True)
 
+        copy_stream = torch.cuda.Stream(device)
+        use_fused = [False]
+        bucket_evs = [torch.cuda.Event() for _ in range(L.nbuckets)]
+
         def e2e_step():
-            for o in range(0, L.padded, win):
-                n = min(win, L.padded - o)
-                opt.grads_flat[o:o + n].copy_(host[:n], non_blocking=True)
-            (fused_fn if (fused_fn is not None and ms_fused < ms_nccl) else opt.step)()
+            main = torch.cuda.current_stream(device)
+            copy_stream.wait_stream(main)        # the previous step is done with the gradient buffer
+            with torch.cuda.stream(copy_stream):
+                for b in range(L.nbuckets):
+                    lo, hi = L.bucket_range(b)
+                    for o in range(lo, hi, win):
+                        n = min(win, hi - o)
+                        opt.grads_flat[o:o + n].copy_(host[:n], non_blocking=True)
+                    bucket_evs[b].record(copy_stream)
+            if use_fused[0]:                     # one kernel over everything: it can only start after the last copy
+                main.wait_stream(copy_stream)
+                fused_fn()
+            else:                                # bucket b's reduce-scatter starts as soon as bucket b has landed
+                opt.step_count += 1
+                opt.noop.zero_()
+                for b in range(L.nbuckets):
+                    main.wait_event(bucket_evs[b])
+                    opt.reduce_gradients([b], side_stream=True)
+                opt.update_and_gather(float(world))
             host_flag.copy_(opt.noop, non_blocking=True)
-            torch.cuda.current_stream(device).synchronize()
+            main.synchronize()
 
         e2e_step()
         ms_e2e, _, _ = _timed(e2e_step, max(2, min(args.steps, 3)), device)
+        e2e_routes = {"nccl_bucket_overlapped": ms_e2e}
+        if fused_fn is not None:
+            use_fused[0] = True
+            e2e_step()
+            ms_f, _, _ = _timed(e2e_step, max(2, min(args.steps, 3)), device)
+            e2e_routes["fused_after_last_copy"] = ms_f
+            ms_e2e = min(ms_e2e, ms_f)
         e2e = {"value": P / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 2 * L.padded * world,
-               "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e,
-               "note": "each rank copies its full bf16 gradient buffer from pinned host memory every step, then "
-                       "reduce-scatter -> update -> all-gather; the skip flag is read back; bytes are summed over ranks"}
+               "d2h_bytes_per_step": 4 * world, "ms_per_step": ms_e2e, "routes_ms": e2e_routes,
+               "note": "each rank copies its full bf16 gradient buffer from pinned host memory every step, bucket by "
+                       "bucket on a copy stream; on the NCCL route a bucket's reduce-scatter starts as soon as the bucket "
+                       "has landed (the fused one-kernel route has to wait for the last copy); the skip flag is read "
+                       "back; bytes are summed over ranks"}
     if sampler:
         sampler.stop()
+    parity = parity_block(amp_C, rank, world, device)
     if rank == 0:
         peak, peak_src = peaks()
         shard_bytes = BYTES_PER_PARAM * L.state_elems
@@ -159,7 +274,7 @@ def run_distributed(args, rank, world, local_rank, device):
             "nvlink": {"bytes_sent_per_gpu_per_collective": nvlink_bytes,
                        "reduce_scatter_GBps_per_gpu": nvlink_bytes / (ms_rs * 1e-3) / 1e9,
                        "all_gather_GBps_per_gpu": nvlink_bytes / (ms_ag * 1e-3) / 1e9},
-            "clocks": clocks, "gpu_launches": int(launches),
+            "clocks": clocks, "gpu_launches": int(launches), "parity": parity,
             "e2e": e2e if e2e is not None else {"value": None, "unit": UNIT, "h2d_bytes_per_step": None,
                                                 "d2h_bytes_per_step": None, "note": "skipped (--no-e2e)"},
         }

@@ -11,14 +11,14 @@ import torch.distributed as dist
 
 import workloads
 from bench_dist import _timed
-from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
+from beforeholiday_b200.contrib.optimizers import FlatShardedAdam as DistributedFusedAdam
 
 rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(lr)
 dev = torch.device("cuda", lr)
 dist.init_process_group("nccl", device_id=dev)
 numels = workloads.numels(workloads.llama3_8b())
-opt = DistributedFusedAdam(numels=numels, lr=1e-4, betas=(0.9, 0.95), weight_decay=0.1, device=dev, fused_p2p=True)
+opt = DistributedFusedAdam(numels, lr=1e-4, betas=(0.9, 0.95), weight_decay=0.1, device=dev, fused_p2p=True)
 opt.params_flat.normal_(0, 0.02)
 opt.init_master_from_params()
 opt.grads_flat.normal_(0, 1e-3)
