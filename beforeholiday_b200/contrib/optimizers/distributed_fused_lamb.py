@@ -22,8 +22,19 @@ All arithmetic is in libmt_b200.so; there is no CPU path.
 Differences from the reference, on purpose: (1) the learning rate is read from ``param_groups[0]['lr']`` every step
 (the reference keeps ``self._lr`` at its initial 0.0 unless the caller pokes it, :132,744); (2) a parameter with several
 fragments on one rank contributes the SUM of their update norms (the reference's ``scatter_`` keeps one of them,
-:689); (3) ``clip_after_ar=False`` and ``e5m2_allgather=True`` are not carried over (NotImplementedError);
-(4) ``dwu_group_size`` / ``dwu_num_*_pg`` describe a multi-node hierarchy and are accepted and ignored on one node.
+:689); (3) ``dwu_group_size`` / ``dwu_num_*_pg`` describe a multi-node hierarchy and are accepted and ignored on one
+node; (4) with ``clip_after_ar=False`` the overflow decision, which the reference takes per rank from its LOCAL gradient
+norm (:697-703 with :626-632), is all-reduced so that every rank skips or applies the same step.
+
+Options honoured as in the reference:
+  overlap_reductions     post-backward hooks start a bucket's reduce-scatter (own stream) as soon as every gradient of
+                         the bucket has been produced in a non-accumulation backward pass (:249-301, :783-797);
+                         complete_reductions() reduces what is left and forms the norm
+  clip_after_ar=False    the LOCAL gradients are clipped by their own norm and pre-divided by the world size before a SUM
+                         reduce-scatter; stage 1 then does not clip (:629-646, :697)
+  e5m2_allgather=True    stage 2 writes the new parameters as one e5m2 byte each (reference packing, :34-53 of
+                         multi_tensor_distopt_lamb_kernel.cu), the all-gather moves half the bytes, and one converting
+                         launch per bucket unpacks them into the model parameters (:270, :320, :850-866)
 """
 from __future__ import annotations
 
@@ -44,10 +55,8 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         defaults = dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps, weight_decay=weight_decay,
                         grad_averaging=grad_averaging, max_grad_norm=max_grad_norm)
         super().__init__(params, defaults)
-        if e5m2_allgather:
-            raise NotImplementedError("e5m2_allgather belongs to the reference's deprecated fused_adam_cuda packing")
-        if not clip_after_ar:
-            raise NotImplementedError("clip_after_ar=False (clip the local gradients before the reduction) is not carried over")
+        self._e5m2_allgather = bool(e5m2_allgather)
+        self._clip_after_ar = bool(clip_after_ar)
         self._adam_w_mode = 1 if adam_w_mode else 0
         self._use_nvlamb = bool(use_nvlamb)
         self._step_supports_amp_scaling = step_supports_amp_scaling
@@ -82,8 +91,16 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         self.frags = self.layout.fragments()
         self._alloc()
         self._build_launch_sets()
+        self.rs_stream = None
         self._init_comm()
         self._adopt_params()
+        self._bucket_reduced = [False] * self.layout.nbuckets
+        self._rs_events = {}
+        self._grads_generated = set()
+        self._in_backward = False
+        self._hooks = []
+        if self._overlap and self._clip_after_ar and self.world > 1:
+            self._register_hooks()
 
     # ---- buffers --------------------------------------------------------------------------------------------------
     def _alloc(self):
@@ -100,6 +117,8 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         self._global_scale = None
         self._L2_grad_norm = None
         self._one = torch.ones(1, dtype=torch.float32, device=dev)
+        # e5m2_allgather: what the all-gather moves is this byte buffer; params_flat is unpacked from it afterwards
+        self._params_e5m2 = z(L.padded, torch.uint8) if self._e5m2_allgather else None
 
     def _build_launch_sets(self):
         """Tensor lists over ALL owned fragments (fragment order = flat order, so the fragments of one parameter are
@@ -111,7 +130,7 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
             n = f.flat_hi - f.flat_lo
             s = slice(f.state_lo, f.state_lo + n)
             g.append(self.grads_flat[f.flat_lo:f.flat_hi])
-            c.append(self.params_flat[f.flat_lo:f.flat_hi])
+            c.append((self._params_e5m2 if self._e5m2_allgather else self.params_flat)[f.flat_lo:f.flat_hi])
             p.append(self._fp32_p[s]); m.append(self._fp32_m[s]); v.append(self._fp32_v[s]); u.append(self._fp32_u[s])
         self._stage1_lists = [g, p, m, v, u]
         self._stage2_lists = [u, p, c]
@@ -151,6 +170,7 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
             ranks = list(range(dist.get_world_size())) if self.group is None else dist.get_process_group_ranks(self.group)
             self.ag_group = dist.new_group(ranks=ranks, backend="nccl")   # all-gathers overlap stage 2 of the next bucket
             self.ag_stream = torch.cuda.Stream(self.device)
+            self.rs_stream = torch.cuda.Stream(self.device)               # reduce-scatters started from backward hooks
 
     def _adopt_params(self):
         """Model tensors become views of the flat buffers (parameters AND gradients), masters are initialised from them
@@ -174,15 +194,24 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         lo, hi = L.bucket_range(b)
         olo, ohi = L.owned_range(b)
         if self.world > 1:
-            dist.reduce_scatter_tensor(self.grads_flat[olo:ohi], self.grads_flat[lo:hi], op=dist.ReduceOp.AVG,
-                                       group=self.rs_group)
+            # clip_after_ar=False pre-divided the local gradients by the world size itself (:642-643)
+            op = dist.ReduceOp.AVG if self._clip_after_ar else dist.ReduceOp.SUM
+            dist.reduce_scatter_tensor(self.grads_flat[olo:ohi], self.grads_flat[lo:hi], op=op, group=self.rs_group)
 
     def _all_gather(self, b: int):
         L = self.layout
         lo, hi = L.bucket_range(b)
         olo, ohi = L.owned_range(b)
+        buf = self._params_e5m2 if self._e5m2_allgather else self.params_flat
         if self.world > 1:
-            dist.all_gather_into_tensor(self.params_flat[lo:hi], self.params_flat[olo:ohi], group=self.ag_group)
+            dist.all_gather_into_tensor(buf[lo:hi], buf[olo:ohi], group=self.ag_group)
+        if self._e5m2_allgather:
+            self._unpack_e5m2(b)
+
+    def _unpack_e5m2(self, b: int):
+        """Gathered e5m2 bytes of bucket b -> model parameters (one converting launch; skipped on overflow)."""
+        lo, hi = self.layout.bucket_range(b)
+        self._amp_C().maybe_cast_mt(8192, self._overflow_buf, [[self._params_e5m2[lo:hi]], [self.params_flat[lo:hi]]])
 
     def _all_reduce(self, t, op=dist.ReduceOp.SUM):
         if self.world > 1:
@@ -205,7 +234,9 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
     def _stage1(self, global_scale, global_grad_norm, max_grad_norm) -> Optional[torch.Tensor]:
         if not self.frags:
             return None
-        extra = (self._seg_begin, self.model_dtype) if self._any_rank_needs_norms else ()
+        # the dtype whose rounding of the master IS the model parameter: its norm is taken from the masters
+        norm_dt = torch.uint8 if self._e5m2_allgather else self.model_dtype
+        extra = (self._seg_begin, norm_dt) if self._any_rank_needs_norms else ()
         return self._amp_C().multi_tensor_lamb_compute_update_term(
             8192, self._overflow_buf, self._stage1_lists, self._beta1, self._beta2, self._beta3, self._bias_correction,
             self._step, self._eps, self._adam_w_mode, self._decay, global_scale, global_grad_norm, max_grad_norm, *extra)
@@ -240,12 +271,103 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
     def zero_grad(self, set_to_none: bool = False):
         # the gradients are views of the flat buffer: they are cleared, never dropped
         self.grads_flat.zero_()
+        for p, o in zip(self._model_params, self.layout.offsets):
+            if p.grad is None or p.grad.data_ptr() != self.grads_flat[o:o + 1].data_ptr():
+                p.grad = self.grads_flat[o:o + p.numel()].view(p.shape)
+
+    # ---- gradient reductions ---------------------------------------------------------------------------------------------
+    def _register_hooks(self):
+        """overlap_reductions: one post-accumulate hook per parameter (reference :249-301)."""
+        L = self.layout
+        B = L.bucket_elems
+        sizes = [p.numel() for p in self._model_params]
+        self._param_buckets = [list(range(o // B, (o + max(n, 1) - 1) // B + 1)) for o, n in zip(L.offsets, sizes)]
+        self._bucket_params = [[] for _ in range(L.nbuckets)]
+        for i, bs in enumerate(self._param_buckets):
+            for b in bs:
+                self._bucket_params[b].append(i)
+        for i, p in enumerate(self._model_params):
+            self._hooks.append(p.register_post_accumulate_grad_hook(lambda param, i=i: self._on_grad_ready(i)))
+
+    def _on_grad_ready(self, i):
+        """Reference `_do_overlapped_reduction` (:783-797): nothing happens on accumulation steps; otherwise a bucket
+        whose gradients have all arrived in this backward pass is reduce-scattered at once, on its own stream."""
+        if self._is_accumulation_step or self._last_step:
+            return
+        if not self._in_backward:
+            self._in_backward = True
+            self._grads_generated.clear()
+            torch.autograd.Variable._execution_engine.queue_callback(self._on_backward_done)
+        p = self._model_params[i]
+        o = self.layout.offsets[i]
+        if p.grad is None or p.grad.data_ptr() != self.grads_flat[o:o + 1].data_ptr():
+            return          # the gradient was re-allocated by the caller: complete_reductions() will pick it up
+        self._grads_generated.add(i)
+        ready = [b for b in self._param_buckets[i] if not self._bucket_reduced[b]
+                 and all(j in self._grads_generated for j in self._bucket_params[b])]
+        if ready:
+            main = torch.cuda.current_stream(self.device)
+            self.rs_stream.wait_stream(main)
+            with torch.cuda.stream(self.rs_stream):
+                for b in ready:
+                    self._reduce_scatter(b)
+                    e = torch.cuda.Event()
+                    e.record(self.rs_stream)
+                    self._rs_events[b] = e
+                    self._bucket_reduced[b] = True
+
+    def _on_backward_done(self):
+        self._in_backward = False
+        self._grads_generated.clear()
+
+    def _adopt_stray_grads(self):
+        """Gradients that are no longer views of the flat buffer (the caller replaced p.grad) are added back in."""
+        for p, o in zip(self._model_params, self.layout.offsets):
+            view = self.grads_flat[o:o + p.numel()]
+            if p.grad is not None and p.grad.data_ptr() != view.data_ptr():
+                view.add_(p.grad.detach().reshape(-1).to(view.dtype))
+                p.grad = view.view(p.shape)
+
+    def _clip_before_reduction(self):
+        """clip_after_ar=False (reference :629-646): L2 norm of the LOCAL flat gradients; coefficient
+        min(1, loss_scale * max_grad_norm / (1e-6 + norm)), replaced by 1 when it is not finite; the gradients are
+        multiplied by round_fp16(coefficient) / world so that the SUM reduce-scatter yields clipped averages."""
+        flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        norm = self._local_norm(flag)
+        gs = self._device_scalar(1.0 if self._global_scale is None else self._global_scale, "_gs_cache")
+        coeff = gs * float(self.defaults['max_grad_norm']) / (1e-6 + norm)
+        coeff = torch.where(coeff > 1, torch.ones_like(coeff), coeff)
+        coeff = torch.where(coeff + 1 > coeff, coeff, torch.ones_like(coeff))       # nan / inf -> 1 (:639-641)
+        scale = (coeff.half() / self.world).to(self.grads_flat.dtype)
+        self.grads_flat.mul_(scale)
+        return norm
+
+    def _local_norm(self, flag) -> torch.Tensor:
+        n, _ = self._amp_C().multi_tensor_l2norm(65536, flag, [[self.grads_flat]], False)
+        return n
 
     def complete_reductions(self):
-        """Reduce-scatter every bucket and form the global L2 norm of the averaged (still loss-scaled) gradients
-        (reference :590-629, :813-834)."""
+        """Reduce-scatter every bucket that has not been reduced during backward and form the L2 gradient norm
+        (reference :590-671, :813-834): the global norm of the averaged, still loss-scaled gradients -- or, with
+        clip_after_ar=False, this rank's local norm, taken before the clipped gradients are reduced."""
+        self._adopt_stray_grads()
+        local_norm = None
+        if not self._clip_after_ar:
+            local_norm = self._clip_before_reduction()
+        main = torch.cuda.current_stream(self.device) if self.device.type == "cuda" else None
+        for e in self._rs_events.values():
+            main.wait_event(e)
+        self._rs_events.clear()
         for b in range(self.layout.nbuckets - 1, -1, -1):
-            self._reduce_scatter(b)
+            if not self._bucket_reduced[b]:
+                self._reduce_scatter(b)
+        self._bucket_reduced = [False] * self.layout.nbuckets
+        if local_norm is not None:
+            # every rank must take the same skip decision: share whether ANY local norm was non-finite
+            bad = (~(local_norm + 1 > local_norm)).to(torch.float32)
+            self._all_reduce(bad, op=dist.ReduceOp.MAX)
+            self._L2_grad_norm = torch.where(bad > 0, torch.full_like(local_norm, float("inf")), local_norm)
+            return
         sq = self._shard_sq_norm()
         self._all_reduce(sq)
         self._L2_grad_norm = sq.sqrt()
@@ -261,7 +383,8 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
 
     def _pipeline_step(self):
         gs = self._device_scalar(1.0 if self._global_scale is None else self._global_scale, "_gs_cache")
-        max_grad_norm = float(self.defaults['max_grad_norm'])
+        # clipping before the reduction already happened in complete_reductions(): stage 1 must not clip again (:697)
+        max_grad_norm = float(self.defaults['max_grad_norm']) if self._clip_after_ar else 0.0
         gnorm = self._L2_grad_norm
         assert gnorm is not None, "call complete_reductions() before step()"
         # overflow <=> the global norm is inf/nan; identical on every rank because the norm was all-reduced (:702-710)

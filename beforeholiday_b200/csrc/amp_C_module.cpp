@@ -37,6 +37,7 @@ int dtype_tag(at::ScalarType t, const char* who) {
         case at::ScalarType::Half: return MT_F16;
         case at::ScalarType::BFloat16: return MT_BF16;
         case at::ScalarType::Double: return MT_F64;
+        case at::ScalarType::Byte: return MT_E5M2;  // e5m2 packing; only the sharded-LAMB copy / unpack ops take it
         default: TORCH_CHECK(false, who, ": unsupported dtype ", t);
     }
     return -1;
@@ -521,8 +522,9 @@ py::object multi_tensor_lamb_compute_update_term(int chunk_size, at::Tensor noop
         nseg = (int)seg_begin->numel() - 1;
         seg = seg_begin->data_ptr<int32_t>();
         const at::ScalarType md = model_dtype.has_value() ? model_dtype.value() : at::kFloat;
-        mdt = md == at::kHalf ? MT_F16 : md == at::kBFloat16 ? MT_BF16 : MT_F32;
-        TORCH_CHECK(md == at::kHalf || md == at::kBFloat16 || md == at::kFloat, "model_dtype must be float32, float16 or bfloat16");
+        mdt = md == at::kHalf ? MT_F16 : md == at::kBFloat16 ? MT_BF16 : md == at::kByte ? MT_E5M2 : MT_F32;
+        TORCH_CHECK(md == at::kHalf || md == at::kBFloat16 || md == at::kFloat || md == at::kByte,
+                    "model_dtype must be float32, float16, bfloat16, or uint8 for parameters that travel e5m2-packed");
         out = at::zeros({2, nseg}, f.first.options().dtype(at::kFloat).layout(at::kStrided));
         sbytes = mt_dist_lamb_scratch_bytes(&f.tl);
         scratch = at::empty({(int64_t)(sbytes ? sbytes : 4)}, f.first.options().dtype(at::kByte).layout(at::kStrided));

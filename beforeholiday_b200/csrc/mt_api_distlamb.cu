@@ -104,8 +104,12 @@ extern "C" int mt_multi_tensor_lamb_compute_update_term(
     }
     // Tn only matters with need_norms; without it one instantiation per gradient type is enough
     const int mdt = need_norms ? model_dtype : MT_F32;
-    MT_DISPATCH_FHB(tl->dtype[0], Tg, "multi_tensor_lamb_compute_update_term",
-        MT_DISPATCH_FHB(mdt, Tn, "multi_tensor_lamb_compute_update_term", MT_DL1(Tg, Tn)))
+    if (mdt == MT_E5M2) {  // the model parameters are the e5m2-rounded masters (e5m2_allgather): norm them as such
+        MT_DISPATCH_FHB(tl->dtype[0], Tg, "multi_tensor_lamb_compute_update_term", MT_DL1(Tg, e5m2_t))
+    } else {
+        MT_DISPATCH_FHB(tl->dtype[0], Tg, "multi_tensor_lamb_compute_update_term",
+            MT_DISPATCH_FHB(mdt, Tn, "multi_tensor_lamb_compute_update_term", MT_DL1(Tg, Tn)))
+    }
 #undef MT_DL1
     if (rc) return rc;
     if (need_norms && tb.ntiles > 0) {
@@ -134,6 +138,12 @@ extern "C" int mt_multi_tensor_lamb_update_weights(int chunk_size, int32_t* noop
     TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
+    if (tl->dtype[2] == MT_E5M2) {  // reference DISPATCH_FLOAT_HALF_AND_BYTE (:489): the e5m2_allgather packing
+        using Op = DistLambStage2Op<e5m2_t>;
+        typename Op::Params prm{per_tensor_param_norm, per_tensor_update_norm, update_norm_offset, learning_rate,
+                                per_tensor_decay, use_nvlamb};
+        return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+    }
     MT_DISPATCH_FHB(tl->dtype[2], Tc, "multi_tensor_lamb_update_weights", {
         using Op = DistLambStage2Op<Tc>;
         typename Op::Params prm{per_tensor_param_norm, per_tensor_update_norm, update_norm_offset, learning_rate,

@@ -36,6 +36,13 @@ extern "C" int mt_multi_tensor_maybe_cast(int chunk_size, int32_t* noop_flag, co
     TableRef tb;
     rc = get_table(tl, choose_tile_elems(tl, tl->device), stream, &tb);
     if (rc) return rc;
+    if (tl->dtype[0] == MT_E5M2) {  // unpack of the e5m2 all-gather (fused_adam_cuda_kernel.cu:417-463)
+        MT_DISPATCH_FHB(tl->dtype[1], Tout, "maybe_cast_mt", {
+            using Op = CastOp<e5m2_t, Tout>;
+            typename Op::Params prm{0};
+            return launch_table_kernel<Op, kG, kU, kThreads, kMinBlocks>(tb, prm, noop_flag, tl->device, stream);
+        })
+    }
     MT_DISPATCH_FHB(tl->dtype[0], Tin, "maybe_cast_mt",
         MT_DISPATCH_FHB(tl->dtype[1], Tout, "maybe_cast_mt", {
             using Op = CastOp<Tin, Tout>;

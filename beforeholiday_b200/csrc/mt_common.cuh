@@ -76,6 +76,24 @@ template <> struct Elem<__nv_bfloat16> {
     __device__ static __forceinline__ float round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
 };
 
+// One-byte e5m2 packing of the reference's `e5m2_allgather` option
+// (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:34-66): the byte is the high byte of
+// half(v + 2^floor(log2|v|) / 8) -- half an e5m2 ulp is added in magnitude before the fp16 rounding, then the low
+// mantissa byte is dropped -- and unpacks as the high byte of an fp16 whose low byte is zero.
+struct e5m2_t { uint8_t b; };
+__device__ __forceinline__ uint8_t float_to_e5m2(float v) {
+    const float pow2 = __uint_as_float(__float_as_uint(v) & 0xFF800000u);
+    const __half h = __float2half_rn(fadd(v, fmul(pow2, 0.125f)));
+    return (uint8_t)(__half_as_ushort(h) >> 8);
+}
+__device__ __forceinline__ float e5m2_to_float(uint8_t b) { return __half2float(__ushort_as_half((unsigned short)(b << 8))); }
+template <> struct Elem<e5m2_t> {
+    static constexpr int kBytes = 1;
+    __device__ static __forceinline__ float load(const e5m2_t* p) { return e5m2_to_float(p->b); }
+    __device__ static __forceinline__ void store(e5m2_t* p, float v) { p->b = float_to_e5m2(v); }
+    __device__ static __forceinline__ float round(float v) { return e5m2_to_float(float_to_e5m2(v)); }
+};
+
 // ------------------------------------------------------------------------------------------------
 // Raw vector accesses (N 32-bit words).  Streaming data is touched exactly once per step, so nothing is
 // allocated in L1 (L1::no_allocate).  The non-coherent (.nc) path is deliberately NOT used even for input-only
@@ -184,6 +202,21 @@ template <int G, bool RO> struct Group<__nv_bfloat16, G, RO> {
             w[i] = *reinterpret_cast<uint32_t*>(&h);
         }
         RawVec<G / 2, RO>::st(p, w);
+    }
+};
+template <int G, bool RO> struct Group<e5m2_t, G, RO> {  // 8 elements = 8 bytes
+    static_assert(G == 8, "e5m2 lists move 8 elements per access");
+    __device__ static __forceinline__ void ld(const e5m2_t* p, float (&f)[G]) {
+        uint32_t w[2];
+        RawVec<2, RO>::ld(p, w);
+#pragma unroll
+        for (int i = 0; i < 8; i++) f[i] = e5m2_to_float((uint8_t)(w[i >> 2] >> (8 * (i & 3))));
+    }
+    __device__ static __forceinline__ void st(e5m2_t* p, const float (&f)[G]) {
+        uint32_t w[2] = {0u, 0u};
+#pragma unroll
+        for (int i = 0; i < 8; i++) w[i >> 2] |= (uint32_t)float_to_e5m2(f[i]) << (8 * (i & 3));
+        RawVec<2, RO>::st(p, w);
     }
 };
 template <int G, bool RO> struct Group<double, G, RO> {  // rare (Adam dispatches on double); 32-B pieces

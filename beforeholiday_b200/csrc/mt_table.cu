@@ -54,7 +54,7 @@ int validate_lists(const MtTensorLists* tl, int lo, int hi, const char* who) {
     if (tl->ntensors > 0x7fffffff) return set_error(MT_EINVAL, "%s: too many tensors", who);
     if (!tl->ptrs || !tl->numel) return set_error(MT_EINVAL, "%s: ptrs / numel arrays are NULL", who);
     for (int d = 0; d < tl->depth; d++)
-        if (tl->dtype[d] < MT_F32 || tl->dtype[d] > MT_F64)
+        if (tl->dtype[d] < MT_F32 || tl->dtype[d] > MT_E5M2)
             return set_error(MT_EINVAL, "%s: list %d has unknown dtype tag %d", who, d, tl->dtype[d]);
     return MT_OK;
 }

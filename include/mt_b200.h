@@ -17,7 +17,7 @@
  *     thread-local message (the pybind layer raises RuntimeError with it, mirroring TORCH_CHECK).
  *   - `chunk_size` is accepted for signature compatibility.  It only has semantic meaning for the
  *     norm ops, where the overflow flag is defined per chunk (see mt_multi_tensor_l2norm).
- *   - dtype tags: MT_F32, MT_F16, MT_BF16, MT_F64.
+ *   - dtype tags: MT_F32, MT_F16, MT_BF16, MT_F64 (and MT_E5M2 where an entry point says so).
  *   - There is no CPU fallback: on a machine without a CUDA device every compute entry point
  *     returns MT_ECUDA.
  */
@@ -33,7 +33,10 @@ extern "C" {
 
 #define MT_MAX_DEPTH 5
 
-enum { MT_F32 = 0, MT_F16 = 1, MT_BF16 = 2, MT_F64 = 3 };
+enum { MT_F32 = 0, MT_F16 = 1, MT_BF16 = 2, MT_F64 = 3, MT_E5M2 = 4 };
+/* MT_E5M2: one byte per element, the high byte of an fp16 value rounded as the reference's e5m2_allgather packing does
+ * (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:34-66).  Accepted only as the copy list of
+ * mt_multi_tensor_lamb_update_weights and as the input list of mt_multi_tensor_maybe_cast. */
 
 enum {
     MT_OK = 0,

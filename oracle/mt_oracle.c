@@ -33,7 +33,7 @@
 #include <omp.h>
 #endif
 
-enum { DT_F32 = 0, DT_F16 = 1, DT_BF16 = 2, DT_F64 = 3 };
+enum { DT_F32 = 0, DT_F16 = 1, DT_BF16 = 2, DT_F64 = 3, DT_E5M2 = 4 };
 
 /* ---------------------------------------------------------------- 16-bit conversions */
 
@@ -92,8 +92,19 @@ static inline uint16_t f32_to_bf16(float f) {
 }
 static inline float bf16_to_f32(uint16_t h) { return u2f((uint32_t)h << 16); }
 
+/* e5m2 packing of the reference's e5m2_allgather (apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:34-66,
+ * fused_adam_cuda_kernel.cu:396-428): the byte is the HIGH byte of the fp16 value of (v + 2^floor(log2|v|) / 8), i.e.
+ * half an e5m2 ulp is added in magnitude before the fp16 rounding and the low mantissa byte is dropped; unpacking puts
+ * the byte back as the high byte of an fp16 with a zero low byte. */
+static inline uint8_t f32_to_e5m2(float v) {
+    const float pow2 = u2f(f2u(v) & 0xFF800000u);
+    return (uint8_t)(f32_to_f16(v + pow2 / 8.0f) >> 8);
+}
+static inline float e5m2_to_f32(uint8_t b) { return f16_to_f32((uint16_t)((uint16_t)b << 8)); }
+
 static inline float ld(const void* p, int dt, int64_t i) {
     switch (dt) {
+        case DT_E5M2: return e5m2_to_f32(((const uint8_t*)p)[i]);
         case DT_F32: return ((const float*)p)[i];
         case DT_F16: return f16_to_f32(((const uint16_t*)p)[i]);
         case DT_BF16: return bf16_to_f32(((const uint16_t*)p)[i]);
@@ -102,6 +113,7 @@ static inline float ld(const void* p, int dt, int64_t i) {
 }
 static inline void st(void* p, int dt, int64_t i, float v) {
     switch (dt) {
+        case DT_E5M2: ((uint8_t*)p)[i] = f32_to_e5m2(v); break;
         case DT_F32: ((float*)p)[i] = v; break;
         case DT_F16: ((uint16_t*)p)[i] = f32_to_f16(v); break;
         case DT_BF16: ((uint16_t*)p)[i] = f32_to_bf16(v); break;
@@ -113,6 +125,7 @@ static inline float rnd(float v, int dt) {
     switch (dt) {
         case DT_F16: return f16_to_f32(f32_to_f16(v));
         case DT_BF16: return bf16_to_f32(f32_to_bf16(v));
+        case DT_E5M2: return e5m2_to_f32(f32_to_e5m2(v));
         default: return v;
     }
 }
@@ -325,7 +338,7 @@ static float l2norm_chunk(const void* x, int dt, int64_t off, int64_t n, int chu
     return block_reduce_512(part);
 }
 
-static int esize(int dt) { return dt == DT_F32 ? 4 : (dt == DT_F64 ? 8 : 2); }
+static int esize(int dt) { return dt == DT_F32 ? 4 : (dt == DT_F64 ? 8 : (dt == DT_E5M2 ? 1 : 2)); }
 
 /* multi_tensor_l2norm_cuda: csrc/multi_tensor_l2norm_kernel.cu:301-364 with the 320-block / 110-tensor
  * launcher of csrc/multi_tensor_apply_base.cuh:16-17,84-143 and cleanup (:198-237).

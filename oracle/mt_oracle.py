@@ -21,7 +21,7 @@ import torch
 _HERE = Path(__file__).resolve().parent
 _LIB = None
 
-DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2, torch.float64: 3}
+DT = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2, torch.float64: 3, torch.uint8: 4}   # uint8 = e5m2 packing
 
 
 def build(force: bool = False) -> Path:

@@ -3,6 +3,7 @@ this repo's drop-in class on real GPUs: NCCL process groups of 2 and 4 ranks, th
 pipeline, post-backward hooks that reduce-scatter buckets while backward is still running, GradScaler with device-side
 skip, gather-on-root checkpoints; plus the one-kernel NVLink route (fused_p2p) on a bf16 model.  Skipped on a 1-GPU
 box (run with `gpurun --gpus 2|4`); the CPU twin (gloo + oracle) is tests/test_dist_adam_cpu.py."""
+import datetime
 import os
 import socket
 import sys
@@ -30,7 +31,8 @@ def _worker(rank, world, port, outdir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
     dev = torch.device("cuda", rank)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    # a case that fails on one rank only leaves the ranks in different collectives: keep the resulting hang short
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev, timeout=datetime.timedelta(seconds=120))
     results = {}
     try:
         from beforeholiday_b200.contrib.optimizers import DistributedFusedAdam
@@ -42,6 +44,8 @@ def _worker(rank, world, port, outdir):
                 ok = torch.ones(1, device=dev)
             except Exception:  # noqa: BLE001
                 results[name] = traceback.format_exc()
+                with open(os.path.join(outdir, f"rank{rank}.{name}.err"), "w") as f:   # survives a later hang / abort
+                    f.write(results[name])
                 ok = torch.zeros(1, device=dev)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             if name not in results:
@@ -82,7 +86,8 @@ def _results(world, tmp_path_factory):
         for p in procs:
             if p.exitcode is None:
                 p.kill()
-        assert all(c == 0 for c in codes), f"worker exit codes {codes}"
+        errs = "".join(f"--- {f.name} ---\n{f.read_text()[-3000:]}\n" for f in sorted(out.glob("rank*.err")))
+        assert all(c == 0 for c in codes), f"worker exit codes {codes}\n{errs}"
         _cache[world] = [torch.load(out / f"rank{r}.pt") for r in range(world)]
     return _cache[world]
 

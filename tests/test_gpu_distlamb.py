@@ -130,6 +130,49 @@ def test_update_weights_matches_oracle(amp_C, oracle, copy_t, use_nvlamb):
             assert bits_equal(a, b), f"list {li} tensor {i}: {n_mismatch(a, b)} mismatches"
 
 
+@pytest.mark.parametrize("use_nvlamb", [False, True])
+def test_update_weights_e5m2_copy_matches_oracle(amp_C, oracle, use_nvlamb):
+    """e5m2_allgather: the copy list is one byte per element, packed as the reference does
+    (multi_tensor_distopt_lamb_kernel.cu:34-53, dispatch :489) -- NOT torch's round-to-nearest-even float8_e5m2."""
+    lists = make_lists([F32, F32, F32], SIZES, seed=37, scale=0.1)
+    lists[2] = [torch.zeros(t.numel(), dtype=torch.uint8) for t in lists[2]]
+    n = len(SIZES)
+    wd = _hyper(n)[5]
+    lg, lc = to_gpu(lists), cpu_clone(lists)
+    pn = torch.tensor([1.5, 0.0, 2.0, 3.0, 0.7, 1.0, 9.0, 4.0])
+    un = torch.tensor([0.5, 0.25, 0.0, 2.0, 1.0])
+    off = torch.tensor([0, 1, 1, 2, 3, 3, 3, 4], dtype=torch.int64)
+    lr = torch.tensor([2e-3])
+    fg, fc = torch.zeros(1, dtype=torch.int32, device="cuda"), torch.zeros(1, dtype=torch.int32)
+    d = lambda t: t.cuda()
+    amp_C.multi_tensor_lamb_update_weights(8192, fg, lg, d(pn), d(un), d(off), d(lr), d(wd), d(lr), use_nvlamb)
+    oracle.multi_tensor_lamb_update_weights(8192, fc, lc, pn, un, off, lr, wd, lr, use_nvlamb)
+    for i, (a, b) in enumerate(zip(lg[1], lc[1])):
+        assert bits_equal(a, b)
+    for i, (a, b) in enumerate(zip(lg[2], lc[2])):
+        assert torch.equal(a.cpu(), b), f"tensor {i}: {int((a.cpu() != b).sum())} packed bytes differ"
+    # and it is the reference's round-half-up packing: differs from torch's float8_e5m2 on ties
+    t = torch.tensor([1.125, -1.125, 1.0, 3.0], device="cuda")
+    out = torch.zeros(4, dtype=torch.uint8, device="cuda")
+    amp_C.multi_tensor_lamb_update_weights(8192, fg, [[torch.zeros(4, device="cuda")], [t.clone()], [out]], d(torch.ones(1)),
+                                           d(torch.ones(1)), d(torch.zeros(1, dtype=torch.int64)), d(lr), d(torch.zeros(1)),
+                                           d(lr), False)
+    assert out.tolist() == [0x3D, 0xBD, 0x3C, 0x42]
+
+
+@pytest.mark.parametrize("out_t", [F16, BF16, F32])
+def test_maybe_cast_mt_unpacks_e5m2(amp_C, oracle, out_t):
+    g = torch.Generator().manual_seed(38)
+    packed = [torch.randint(0, 256, (n,), dtype=torch.uint8, generator=g) for n in SIZES]
+    outs = [torch.zeros(n, dtype=out_t) for n in SIZES]
+    lg = [[t.cuda() for t in packed], [t.cuda() for t in outs]]
+    fg = torch.zeros(1, dtype=torch.int32, device="cuda")
+    amp_C.maybe_cast_mt(8192, fg, lg)
+    for a, b in zip(lg[1], packed):
+        want = oracle.convert(oracle.convert(b, F32), out_t)      # byte -> high byte of an fp16 -> out_t
+        assert bits_equal(a, want)
+
+
 def test_flag_set_touches_nothing(amp_C):
     lists = _stage1_lists(F16, 35)
     n = len(SIZES)

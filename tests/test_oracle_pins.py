@@ -405,3 +405,21 @@ def test_legacy_split_lamb_follows_pinned_lamb(oracle, wd, nv):
         assert bits_equal(a, b)
     for a, b in zip(ps, ps2):
         assert rel_close(b, a, 1e-6, 1e-9)
+
+
+def test_e5m2_packing_is_the_reference_formula():
+    """apex/contrib/csrc/optimizers/multi_tensor_distopt_lamb_kernel.cu:34-66: byte = high byte of
+    half(v + 2^floor(log2|v|) / 8); unpack = that byte over a zero low byte.  Restated here with torch ops (fp32 add,
+    round-to-nearest fp16 cast) and compared with the oracle's C over random and edge values."""
+    import torch
+    from oracle import mt_oracle as O
+
+    g = torch.Generator().manual_seed(5)
+    v = torch.cat([torch.randn(20000, generator=g) * 10 ** torch.randint(-6, 5, (20000,), generator=g).float(),
+                   torch.tensor([0.0, -0.0, 1.125, -1.125, 1.0, 65504.0, 70000.0, 6e-8, float("inf"), -float("inf")])])
+    pow2 = (v.view(torch.int32) & -8388608).view(torch.float32)          # 0xFF800000: sign + exponent
+    want = ((v + pow2 / 8.0).half().view(torch.int16).to(torch.int32) >> 8) & 0xFF
+    got = O.convert(v, torch.uint8).to(torch.int32)
+    assert torch.equal(got, want)
+    back = O.convert(got.to(torch.uint8), torch.float32)
+    assert torch.equal(back, (want << 8).to(torch.int16).view(torch.float16).float())

@@ -49,6 +49,19 @@ def timed(fn, steps, device):
 
 
 def nvlink_counters(index):
+    """Cumulative NVLink payload counters of one GPU in KiB: NVML field values (all links summed) when the driver
+    exposes them, else `nvidia-smi nvlink -gt d`.  None when neither answers."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        vals = pynvml.nvmlDeviceGetFieldValues(h, [pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX,
+                                                   pynvml.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX])
+        if all(v.nvmlReturn == 0 for v in vals):
+            return {"tx_kib": int(vals[0].value.ullVal), "rx_kib": int(vals[1].value.ullVal), "source": "nvml"}
+    except Exception:  # noqa: BLE001
+        pass
     try:
         r = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(index)], capture_output=True, text=True, timeout=20)
         tx = rx = 0
@@ -57,9 +70,15 @@ def nvlink_counters(index):
                 tx += int(line.split(":")[-1].split()[0])
             if "Data Rx" in line:
                 rx += int(line.split(":")[-1].split()[0])
-        return {"tx_kib": tx, "rx_kib": rx} if (tx or rx) else None
-    except Exception:  # noqa: BLE001
-        return None
+        if tx or rx:
+            return {"tx_kib": tx, "rx_kib": rx, "source": "nvidia-smi"}
+        nvlink_counters.raw = (r.stdout + r.stderr)[:400]
+    except Exception as e:  # noqa: BLE001
+        nvlink_counters.raw = repr(e)[:200]
+    return None
+
+
+nvlink_counters.raw = None
 
 
 def main():
@@ -137,6 +156,7 @@ def main():
             rec["nvlink_tx_GB_per_step"] = (c1["tx_kib"] - c0["tx_kib"]) * 1024 / 1e9 / args.steps
             rec["nvlink_rx_GB_per_step"] = (c1["rx_kib"] - c0["rx_kib"]) * 1024 / 1e9 / args.steps
         out["fused"][f"ld{ld16}_st{st16}"] = rec
+    out["nvlink_counter_note"] = nvlink_counters.raw
     out["fused_params"] = Pn
     out["fused_link_bytes_ideal_per_dir"] = link_bytes
     if rank == 0:
