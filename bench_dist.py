@@ -163,7 +163,7 @@ def run_distributed(args, rank, world, local_rank, device):
     launches = amp_C.launch_count() - launches0
     clocks = ClockSampler.summarize(sampler.window(t0, t1)) if sampler else None
     ms, route, ms_fused = ms_nccl, "nccl: reduce_scatter -> update -> all_gather, 3 streams", None
-    ms_p2p = ms_mc = None
+    ms_p2p = ms_mc = ms_hy = hybrid_best = hybrid_search = None
     fused_fn = None
     if fused:
         # fused route: one kernel reads the gradient shard from every peer and writes the parameters to every peer
@@ -181,6 +181,23 @@ def run_distributed(args, rank, world, local_rank, device):
             if ms_mc < ms_p2p:
                 ms_fused, fused_fn, t0f, t1f = ms_mc, (lambda: opt.step_fused(multicast=True)), t0m, t1m
                 fused_name = "fused_multicast: one kernel, multimem.ld_reduce / multimem.st through NVSwitch (+2 barriers)"
+            # hybrid: a share of the 32 KB blocks goes peer-to-peer instead of through the switch.  A short search over
+            # the split (2 warm-up + 3 steps each), then the best one is timed like the other routes.
+            search = {}
+            for k16 in (2, 3, 4, 6):
+                fn_h = (lambda k=k16: opt.step_fused(multicast=True, ld_p2p_of16=k, st_p2p_of16=k))
+                for _ in range(2):
+                    fn_h()
+                search[k16], _, _ = _timed(fn_h, 3, device)
+            best = min(search, key=search.get)
+            hybrid_search = {f"{k}/16": v for k, v in search.items()}
+            fn_h = (lambda: opt.step_fused(multicast=True, ld_p2p_of16=best, st_p2p_of16=best))
+            ms_hy, t0h, t1h = _timed(fn_h, args.steps, device)
+            hybrid_best = f"{best}/16"
+            if ms_hy < ms_fused:
+                ms_fused, fused_fn, t0f, t1f = ms_hy, fn_h, t0h, t1h
+                fused_name = (f"fused_hybrid: one kernel, {best}/16 of the 32 KB blocks by peer-to-peer ld/st, the rest by "
+                              "multimem.ld_reduce / multimem.st through NVSwitch (+2 barriers)")
         if ms_fused < ms_nccl:
             ms, route = ms_fused, fused_name
             launches = n_l
@@ -267,7 +284,8 @@ def run_distributed(args, rank, world, local_rank, device):
                          "algorithmic_bytes_per_launch": shard_bytes / max(1, L.nbuckets)},
             "route": route, "fused_p2p_error": fused_err,
             "breakdown_ms": {"step": ms, "step_nccl_overlapped": ms_nccl, "step_fused_p2p": ms_p2p,
-                             "step_fused_multicast": ms_mc,
+                             "step_fused_multicast": ms_mc, "step_fused_hybrid": ms_hy,
+                             "hybrid_best_p2p_share": hybrid_best, "hybrid_search_ms": hybrid_search,
                              "step_nccl_serial": ms_serial, "update_only": ms_update,
                              "reduce_scatter_only": ms_rs, "all_gather_only": ms_ag},
             "update_only": {"params_per_s_whole_job": P / (ms_update * 1e-3), "hbm_gbs_per_gpu": achieved},
