@@ -64,7 +64,8 @@ def matches_pytorch(make, rank, device, num_layers=11, layer_size=7, batch_size=
     torch.manual_seed(1234 + rank)
     ref_model, ref_optim, dist_model, dist_optim = make_models(make, num_layers, layer_size, dtype, param_sync_dtype,
                                                                device, overlap_communication, **extra)
-    assert dist_optim.layout.nbuckets > 1
+    # (sub-shards are 256-element aligned: the reference's 11 x Linear(7, 7) spans several buckets up to world 3)
+    assert dist_optim.layout.nbuckets > 1 or dist.get_world_size() > 3
     for step in range(num_steps):
         ref_optim.zero_grad()
         dist_optim.zero_grad()

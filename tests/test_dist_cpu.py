@@ -137,7 +137,7 @@ def _lamb_cls():
 
         def _reduce_scatter(self, b):
             lo, hi = self.layout.bucket_range(b)
-            buf = self.grads_flat[lo:hi].float() / self.world
+            buf = self.grads_flat[lo:hi].float() / (self.world if self._clip_after_ar else 1)   # AVG, or SUM of pre-divided
             dist.all_reduce(buf, group=self.group)
             olo, ohi = self.layout.owned_range(b)
             self.grads_flat[olo:ohi].copy_(buf[olo - lo:ohi - lo])
@@ -145,9 +145,12 @@ def _lamb_cls():
         def _all_gather(self, b):
             lo, hi = self.layout.bucket_range(b)
             olo, ohi = self.layout.owned_range(b)
+            buf = self._params_e5m2 if self._e5m2_allgather else self.params_flat
             parts = [torch.empty(self.layout.sub_shard, dtype=torch.float32) for _ in range(self.world)]
-            dist.all_gather(parts, self.params_flat[olo:ohi].float().contiguous(), group=self.group)
-            self.params_flat[lo:hi].copy_(torch.cat(parts))
+            dist.all_gather(parts, buf[olo:ohi].float().contiguous(), group=self.group)
+            buf[lo:hi].copy_(torch.cat(parts))
+            if self._e5m2_allgather:
+                self._unpack_e5m2(b)
 
         def _shard_sq_norm(self):
             L = self.layout
@@ -161,10 +164,21 @@ def _lamb_cls():
             sq = O.multi_tensor_lamb_compute_update_term(
                 8192, self._overflow_buf, self._stage1_lists, self._beta1.tolist(), self._beta2.tolist(), None,
                 self._bias_correction.tolist(), int(self._step), self._eps.tolist(), self._adam_w_mode,
-                self._decay.tolist(), float(gs), float(gnorm), max_grad_norm, self.model_dtype)
+                self._decay.tolist(), float(gs), float(gnorm), max_grad_norm,
+                torch.uint8 if self._e5m2_allgather else self.model_dtype)
             seg = self._seg_begin.tolist()
             return torch.stack([torch.stack([sq[s, seg[k]:seg[k + 1]].sum() for k in range(len(seg) - 1)])
                                 for s in range(2)]).float()
+
+        def _local_norm(self, flag):
+            return self.grads_flat.double().norm().float().reshape(1)
+
+        def _unpack_e5m2(self, b):
+            from oracle import mt_oracle as O
+
+            if int(self._overflow_buf) == 0:
+                lo, hi = self.layout.bucket_range(b)
+                self.params_flat[lo:hi].copy_(O.convert(O.convert(self._params_e5m2[lo:hi], torch.float32), self.model_dtype))
 
         def _stage2(self, b, param_norm, update_norm, gnorm):
             from oracle import mt_oracle as O
@@ -178,7 +192,10 @@ def _lamb_cls():
     return CpuShardedLamb
 
 
-def _lamb_worker(rank, world, port, outdir):
+LAMB_OPTIONS = {"default": {}, "e5m2_allgather": {"e5m2_allgather": True}, "clip_before_ar": {"clip_after_ar": False}}
+
+
+def _lamb_worker(rank, world, port, outdir, option="default"):
     import sys
 
     sys.path.insert(0, os.path.dirname(__file__))
@@ -191,7 +208,7 @@ def _lamb_worker(rank, world, port, outdir):
         params = [torch.nn.Parameter((torch.randn(n) * 0.05).bfloat16()) for n in LAMB_SIZES]
         groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
         opt = _lamb_cls()(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, use_nvlamb=False,
-                          dwu_num_blocks=2, dwu_num_chunks=2, device="cpu")
+                          dwu_num_blocks=2, dwu_num_chunks=2, device="cpu", **LAMB_OPTIONS[option])
         assert opt.layout.nbuckets > 1
         assert any(sum(1 for f in opt.frags if f.param == q) > 1 for q in range(len(LAMB_SIZES)))  # multi-fragment runs
         opt.set_global_scale(64.0)
@@ -211,8 +228,8 @@ def _lamb_worker(rank, world, port, outdir):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("world", [2, 4])
-def test_sharded_lamb_matches_single_process(tmp_path, world):
+@pytest.mark.parametrize("world,option", [(2, "default"), (4, "default"), (2, "e5m2_allgather"), (2, "clip_before_ar")])
+def test_sharded_lamb_matches_single_process(tmp_path, world, option):
     import sys
 
     sys.path.insert(0, os.path.dirname(__file__))
@@ -221,7 +238,7 @@ def test_sharded_lamb_matches_single_process(tmp_path, world):
 
     ctx = mp.get_context("spawn")
     port = _free_port()
-    procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    procs = [ctx.Process(target=_lamb_worker, args=(r, world, port, str(tmp_path), option)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -237,7 +254,8 @@ def test_sharded_lamb_matches_single_process(tmp_path, world):
     sizes = [x.numel() for x in order]
     props = [(0.01, 1, 0.9, 0.999, 1e-6)] * len(init[0::2]) + [(0.0, 1, 0.9, 0.999, 1e-6)] * len(init[1::2])
     _, pc, step = replay(O, sizes, order, props, world, 4, torch.bfloat16, 2e-3, 64.0, 1.0, 1, False,
-                         lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2)
+                         lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2, e5m2=(option == "e5m2_allgather"),
+                         clip_after_ar=(option != "clip_before_ar"))
     assert step == 3
     for a, b in zip(res[0], pc):
         ia, ib = a.view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)

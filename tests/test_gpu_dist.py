@@ -281,7 +281,7 @@ def test_flat_bucket_allreduce_two_gpus(tmp_path):
 LAMB_SIZES = [1000, 7, 40000, 333333, 1, 129]
 
 
-def _lamb_worker(rank, world, port, outdir):
+def _lamb_worker(rank, world, port, outdir, option="default"):
     import sys
 
     import torch.distributed as dist
@@ -300,8 +300,9 @@ def _lamb_worker(rank, world, port, outdir):
         init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
         params = [torch.nn.Parameter(x.clone().to(dev)) for x in init]
         groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
+        kw = {"default": {}, "e5m2_allgather": dict(e5m2_allgather=True), "clip_before_ar": dict(clip_after_ar=False)}[option]
         opt = DistributedFusedLAMB(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, dwu_num_blocks=2,
-                                   dwu_num_chunks=2)
+                                   dwu_num_chunks=2, **kw)
         opt.set_global_scale(64.0)
         order = params[0::2] + params[1::2]
         launches = []
@@ -323,8 +324,9 @@ def _lamb_worker(rank, world, port, outdir):
 
 
 @pytest.mark.timeout(600)
-@pytest.mark.parametrize("world", [2, 4])
-def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world):
+@pytest.mark.parametrize("world,option", [(2, "default"), (4, "default"), (2, "e5m2_allgather"), (2, "clip_before_ar"),
+                                          (4, "e5m2_allgather")])
+def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world, option):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import sys
@@ -333,21 +335,27 @@ def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world):
     from lamb_replay import replay
     from oracle import mt_oracle as O
 
-    _run_workers(_lamb_worker, world, tmp_path)
+    _run_workers(_lamb_worker, world, tmp_path, option)
     res = [torch.load(tmp_path / f"rank{r}.pt") for r in range(world)]
     for r in range(1, world):
         for a, b in zip(res[0]["params"], res[r]["params"]):
             assert torch.equal(a.view(torch.int16), b.view(torch.int16))
     assert all(x["step"] == 3 for x in res)
     # l2norm (1 launch) + stage 1 (+ its run finalize) + one stage-2 launch per bucket that holds fragments
-    assert all(n <= 3 + res[0]["nbuckets"] for n in res[0]["launches"]), res[0]["launches"]
+    # (+ one unpack launch per bucket with e5m2_allgather, + the local-norm launch when clipping before the reduction)
+    extra = res[0]["nbuckets"] if option == "e5m2_allgather" else (1 if option == "clip_before_ar" else 0)
+    assert all(n <= 3 + res[0]["nbuckets"] + extra for n in res[0]["launches"]), res[0]["launches"]
     torch.manual_seed(0)
     init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
     order = init[0::2] + init[1::2]
     props = [(0.01, 1, 0.9, 0.999, 1e-6)] * 3 + [(0.0, 1, 0.9, 0.999, 1e-6)] * 3
     _, pc, _ = replay(O, [x.numel() for x in order], order, props, world, 4, torch.bfloat16, 2e-3, 64.0, 1.0, 1, False,
-                      lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2)
+                      lambda it, r, i: 1000 * it + 10 * r + i, overflow_at=2, e5m2=(option == "e5m2_allgather"),
+                      clip_after_ar=(option != "clip_before_ar"))
     for a, b in zip(res[0]["params"], pc):
-        ia, ib = a.reshape(-1).view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
+        if option == "e5m2_allgather":    # two mantissa bits: compare in units of the packing's own step
+            ia, ib = (O.convert(x.reshape(-1).float(), torch.uint8).to(torch.int32) for x in (a, b))
+        else:
+            ia, ib = a.reshape(-1).view(torch.int16).to(torch.int32), b.view(torch.int16).to(torch.int32)
         assert int((ia - ib).abs().max()) <= 1
         assert float((ia != ib).float().mean()) < 0.01

@@ -297,3 +297,53 @@ def test_distributed_fused_lamb_single_gpu_matches_oracle_replay(oracle, dtype, 
     opt._fp32_p.zero_()
     opt.load_state_dict(sd)
     assert torch.equal(opt._fp32_p, sd['fp32_p'])
+
+
+@pytest.mark.parametrize("option", ["e5m2_allgather", "clip_before_ar", "overlap_hooks"])
+@pytest.mark.parametrize("dtype", [F16, BF16])
+def test_distributed_fused_lamb_options_single_gpu(oracle, dtype, option):
+    """The reference's e5m2_allgather / clip_after_ar=False / overlap_reductions options (distributed_fused_lamb.py:88-91,
+    :629-646, :783-797) at world 1 against the oracle replay with the same option: e5m2 parameters are the packed
+    masters (bit-level: the replay packs with the oracle's restatement of the reference formula); clipping before the
+    reduction uses the local norm; with hooks the gradients come from a real backward pass."""
+    from beforeholiday_b200.contrib.optimizers import DistributedFusedLAMB
+    from lamb_replay import make_grad, replay
+
+    torch.manual_seed(0)
+    init = [(torch.randn(n) * 0.05).to(dtype) for n in LAMB_SIZES]
+    params = [torch.nn.Parameter(x.clone().cuda()) for x in init]
+    groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
+    kw = {"e5m2_allgather": dict(e5m2_allgather=True), "clip_before_ar": dict(clip_after_ar=False),
+          "overlap_hooks": dict(overlap_reductions=True)}[option]
+    opt = DistributedFusedLAMB(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, dwu_num_blocks=2,
+                               dwu_num_chunks=2, **kw)
+    opt.set_global_scale(torch.tensor([64.0], device="cuda"))
+    order = params[0::2] + params[1::2]
+    for it in range(3):
+        opt.zero_grad()
+        gs = [make_grad(1000 * it + i, p.numel(), dtype, 64.0).view(p.shape).cuda() for i, p in enumerate(order)]
+        if option == "overlap_hooks":
+            # d/dp sum(p * g) = g: a real backward pass, gradients accumulate into the flat buffer's views
+            sum((p * g).sum() for p, g in zip(order, gs)).backward()
+            assert all(p.grad.data_ptr() == opt.grads_flat[o:o + 1].data_ptr() for p, o in zip(order, opt.layout.offsets))
+        else:
+            for p, g in zip(order, gs):
+                p.grad.copy_(g)
+        opt.complete_reductions()
+        opt.step()
+        assert int(opt._overflow_buf) == 0
+    oi = init[0::2] + init[1::2]
+    props = [(0.01, 1, 0.9, 0.999, 1e-6)] * 3 + [(0.0, 1, 0.9, 0.999, 1e-6)] * 3
+    _, pc, _ = replay(oracle, [x.numel() for x in oi], oi, props, 1, 3, dtype, 2e-3, 64.0, 1.0, 1, False,
+                      lambda it, r, i: 1000 * it + i, e5m2=(option == "e5m2_allgather"),
+                      clip_after_ar=(option != "clip_before_ar"))
+    if option == "e5m2_allgather":
+        # parameters carry two mantissa bits: compare the packed bytes (one e5m2 step = the reference's own granularity)
+        for a, b in zip(order, pc):
+            pa = oracle.convert(a.detach().cpu().reshape(-1).float(), torch.uint8).to(torch.int32)
+            pb = oracle.convert(b.float(), torch.uint8).to(torch.int32)
+            assert torch.equal(oracle.convert(oracle.convert(a.detach().cpu().reshape(-1).float(), torch.uint8), dtype),
+                               a.detach().cpu().reshape(-1))       # really e5m2-representable
+            assert int((pa - pb).abs().max()) <= 1 and float((pa != pb).float().mean()) < 0.01
+    else:
+        _check_vs_replay(order, pc, dtype)
