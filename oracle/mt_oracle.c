@@ -15,13 +15,13 @@
  * against the reference's own CUDA build (--use_fast_math: approximate
  * div/sqrt, FTZ, FMA contraction) they agree to a few ulp.
  *
- * Parity pin: see oracle/README.md -- pinned against (1) the known answers of
- * the reference's unit tests (tests/L0/run_amp/test_multi_tensor_*.py),
- * (2) torch.optim / RefLAMB trajectories on CPU, (3) golden vectors produced by
- * the reference's own CUDA kernels (oracle/_ref) on a B200, committed under
- * tests/golden/.
+ * Parity pin (there is no separate README): (1) the known answers of the reference's unit tests
+ * (tests/L0/run_amp/test_multi_tensor_*.py) and torch.optim / RefLAMB / Novograd trajectories on CPU
+ * (tests/test_oracle_pins.py, fixtures tests/golden/ref_cpu.pt and ref_novograd.pt with their generating scripts);
+ * (2) the reference's own CUDA kernels, compiled unmodified by oracle/build_ref.py into oracle/_ref/ and run beside
+ * this file on the same inputs on a B200 (tests/test_gpu_vs_reference.py) -- live comparison, no stored CUDA goldens.
  *
- * dtype tags: 0 = float32, 1 = float16, 2 = bfloat16, 3 = float64.
+ * dtype tags: 0 = float32, 1 = float16, 2 = bfloat16, 3 = float64, 4 = e5m2 byte packing.
  * Citations are file:line in /root/reference.
  */
 #include <math.h>
@@ -222,7 +222,7 @@ void orc_adam(void* g, void* p, void* m, void* v, int dt, int64_t n,
 /* DistAdamFunctor: apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:103-116.
  * p,m,v are float (acc type), g and the optional p_copy are g_dt.  mode 0: eps under the
  * square root, mode 1: eps outside.  Bias corrections are evaluated in float on the device
- * (:59-63, std::pow(float,int)); powf is used here.  If `noop` is non-NULL and *noop != 0 the
+ * (:59-63, std::pow(float,int), which promotes to double: double pow() here and in the product).  If `noop` is non-NULL and *noop != 0 the
  * update is skipped (product extension; the reference ignores the flag). */
 void orc_dist_adam(float* p, float* m, float* v, const void* g, int g_dt, void* p_copy, int64_t n,
                    float b1, float b2, int bias_correction, float eps, float decay,

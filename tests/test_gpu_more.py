@@ -5,7 +5,7 @@ import pytest
 import torch
 
 from test_gpu_ops import BF16, F16, F32, F64, make_lists, run_both, to_gpu
-from util import bits_equal, cpu_clone, max_rel, n_mismatch, rel_close
+from util import ulp_diff_16, bits_equal, cpu_clone, max_rel, n_mismatch, rel_close
 
 pytestmark = pytest.mark.gpu
 
@@ -63,8 +63,12 @@ def test_novograd(amp_C, oracle, dt, norm_type, mode):
         for a, b in zip(lists_gpu[d], lists_cpu[d]):
             if norm_type == 0:
                 assert bits_equal(a, b), f"list {d}: {n_mismatch(a, b)}"
+            elif dt == F32:
+                assert torch.allclose(a.cpu(), b, rtol=2e-6, atol=1e-9)      # the divisor (blended norm) moved by <= 1e-7
             else:
-                assert torch.allclose(a.float().cpu(), b.float(), rtol=1e-2 if dt != F32 else 1e-5, atol=1e-2 if dt != F32 else 1e-6)
+                # a 1e-7 relative change of the divisor can flip a 16-bit rounding, never more: <= 1 ulp, and rarely
+                assert ulp_diff_16(a, b) <= 1, f"list {d}: {ulp_diff_16(a, b)} ulp"
+                assert n_mismatch(a, b) <= max(2, a.numel() // 200)
 
 
 def test_fused_novograd_runs_and_tracks_norms():
