@@ -1,6 +1,6 @@
 """In-tree build of the native pieces (no JIT cache: the .so files travel with the source tree).
 
-  beforeholiday_b200/libmt_b200.so                      C-ABI CUDA library (nvcc, sm_100a, static cudart)
+  beforeholiday_b200/libmt_b200.so                      C-ABI CUDA library (nvcc, sm_100a, shared cudart)
   beforeholiday_b200/amp_C.cpython-*.so                 pybind11 adaptor over it (g++, torch headers)
 
 `python -m beforeholiday_b200._build` builds both; __graft_entry__.build() calls build_all().
@@ -77,7 +77,10 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
     out = lib_path()
     if force or _newer(out, objs):
         _run([NVCC, "-shared", "-o", str(out)] + [str(o) for o in objs] +
-             ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "static", "-Xcompiler", "-fPIC"])
+             # the runtime is linked dynamically: inside a torch process the loader hands us the libcudart torch has
+             # already mapped (one runtime instance for both), a bare C host finds the toolkit's through the rpath
+             ["-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared", "-Xcompiler", "-fPIC",
+              "-Xlinker", "-rpath", "-Xlinker", "/usr/local/cuda/lib64"])
     return out
 
 

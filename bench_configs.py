@@ -5,7 +5,9 @@ Per config: W >= 3 warm-up steps, then rounds of K steps; every step sits betwee
 launching stream, with an L2 flush (a 256 MiB write, outside the event pair) before it, so small working sets (C1 fits
 L2 many times over) are measured from HBM like the large ones.  Rounds repeat until the config has run for ~0.4 s so
 that the nvidia-smi sampler sees it; `ms` is the median over rounds of the per-round mean step time.  `gbs` =
-bytes_per_param x params / ms with SURVEY 8(d)'s algorithmic bytes; `frac` = gbs / MEASURED_PEAKS hbm_gbs.
+bytes_per_param x params / ms with SURVEY 8(d)'s algorithmic bytes; `frac` = gbs / MEASURED_PEAKS hbm_gbs.  Passes that
+move less than 2 GB also carry `copy_same_bytes_ms`: a plain `dst.copy_(src)` of the same total bytes under the same
+timer -- what this GPU attains at that size, launch latency and ramp included (`frac_of_copy_same_bytes` = that / ms).
 `reference_cuda_ms`: the reference's own kernels (oracle/_ref, compiled unmodified for sm_100a) on the same buffers,
 same timing -- the kernel to beat; measurement infrastructure only, never on the product path.
 """
@@ -109,6 +111,15 @@ def run_configs(amp_C, device, steps, warmup, peak, sampler, summarize, log, wan
                 d["speedup_vs_reference_cuda"] = rms / ms
             except Exception as e:  # noqa: BLE001
                 d["reference_cuda_error"] = repr(e)[:160]
+        if bpp * P < 2e9:
+            # attainable at THIS size: a plain device copy that moves the same number of bytes, timed the same way
+            # (MEASURED_PEAKS' copy figure is taken on 2 GiB+; launch latency and ramp weigh more on a sub-GB pass)
+            half = max(1, int(bpp * P) // 2)
+            src, dst = torch.empty(half, dtype=torch.uint8, device=device), torch.empty(half, dtype=torch.uint8, device=device)
+            cms, _, _, _ = timer(lambda: dst.copy_(src), min_wall_s=0.15)
+            d["copy_same_bytes_ms"] = cms
+            d["frac_of_copy_same_bytes"] = cms / ms
+            del src, dst
         if extra:
             d.update(extra)
         out[name] = d

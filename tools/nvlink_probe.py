@@ -30,7 +30,7 @@ def build_probe():
     src, out = ROOT / "tools" / "nvlink_probe.cu", ROOT / "tools" / "libnvlink_probe.so"
     if not out.exists() or out.stat().st_mtime < src.stat().st_mtime:
         subprocess.run(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
-                        "-shared", "-Xcompiler", "-fPIC", str(src), "-o", str(out)], check=True)
+                        "-shared", "-cudart", "shared", "-Xcompiler", "-fPIC", str(src), "-o", str(out)], check=True)
     return C.CDLL(str(out))
 
 
