@@ -184,20 +184,21 @@ def run_distributed(args, rank, world, local_rank, device):
             # hybrid: a share of the 32 KB blocks goes peer-to-peer instead of through the switch.  A short search over
             # the split (2 warm-up + 3 steps each), then the best one is timed like the other routes.
             search = {}
-            for k16 in (2, 3, 4, 6):
-                fn_h = (lambda k=k16: opt.step_fused(multicast=True, ld_p2p_of16=k, st_p2p_of16=k))
+            for ld16, st16 in ((2, 2), (0, 2), (0, 4), (0, 6)):
+                fn_h = (lambda a=ld16, b=st16: opt.step_fused(multicast=True, ld_p2p_of16=a, st_p2p_of16=b))
                 for _ in range(2):
                     fn_h()
-                search[k16], _, _ = _timed(fn_h, 3, device)
-            best = min(search, key=search.get)
-            hybrid_search = {f"{k}/16": v for k, v in search.items()}
-            fn_h = (lambda: opt.step_fused(multicast=True, ld_p2p_of16=best, st_p2p_of16=best))
+                search[(ld16, st16)], _, _ = _timed(fn_h, 3, device)
+            bl, bs = min(search, key=search.get)
+            hybrid_search = {f"ld {a}/16, st {b}/16": v for (a, b), v in search.items()}
+            fn_h = (lambda: opt.step_fused(multicast=True, ld_p2p_of16=bl, st_p2p_of16=bs))
             ms_hy, t0h, t1h = _timed(fn_h, args.steps, device)
-            hybrid_best = f"{best}/16"
+            hybrid_best = f"ld {bl}/16, st {bs}/16"
             if ms_hy < ms_fused:
                 ms_fused, fused_fn, t0f, t1f = ms_hy, fn_h, t0h, t1h
-                fused_name = (f"fused_hybrid: one kernel, {best}/16 of the 32 KB blocks by peer-to-peer ld/st, the rest by "
-                              "multimem.ld_reduce / multimem.st through NVSwitch (+2 barriers)")
+                fused_name = (f"fused_hybrid: one kernel, {bl}/16 of the gradient loads and {bs}/16 of the parameter stores "
+                              "(32 KB blocks) peer-to-peer, the rest multimem.ld_reduce / multimem.st through NVSwitch "
+                              "(+2 barriers)")
         if ms_fused < ms_nccl:
             ms, route = ms_fused, fused_name
             launches = n_l
