@@ -1,8 +1,9 @@
 """The reference's DistributedFusedAdam test scenarios (apex/contrib/test/optimizers/test_dist_adam.py:84-387) against
 this repo's drop-in class on real GPUs: NCCL process groups of 2 and 4 ranks, the CUDA kernels, the three-stream
 pipeline, post-backward hooks that reduce-scatter buckets while backward is still running, GradScaler with device-side
-skip, gather-on-root checkpoints; plus the one-kernel NVLink route (fused_p2p) on a bf16 model.  Skipped on a 1-GPU
-box (run with `gpurun --gpus 2|4`); the CPU twin (gloo + oracle) is tests/test_dist_adam_cpu.py."""
+skip, gather-on-root checkpoints; plus the one-kernel NVLink route (fused_p2p) on a bf16 model.  World 1 (a one-rank
+NCCL group: the class, its hooks, the scaler protocol and the kernels, without peers) runs on any GPU box; worlds 2 and 4
+need `gpurun --gpus 2|4`.  The CPU twin (gloo + oracle) is tests/test_dist_adam_cpu.py."""
 import datetime
 import os
 import socket
@@ -96,7 +97,7 @@ def _results(world, tmp_path_factory):
 
 
 @pytest.mark.timeout(1200)
-@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("world", [1, 2, 4])
 @pytest.mark.parametrize("case", list(GPU_CASES))
 def test_dist_adam_reference_scenarios_gpu(case, world, tmp_path_factory):
     if torch.cuda.device_count() < world:
