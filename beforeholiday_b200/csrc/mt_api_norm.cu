@@ -104,20 +104,28 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     if (tb.ntiles == 0)  // every tensor empty: zeros, by the small kernel (no tile exists to do it in-launch)
         return launch_norm_finalize(tb, partials, 1, ret, ret_pt, tl->device, stream, mp ? noop_flag : nullptr);
     const NormOut out{partials, ret, ret_pt, sub};
-    // Bytes in flight per thread: 2 groups of 32 B for fp32, 4 groups of 16 B for the 16-bit types (a pure reduction
-    // has registers to spare, and 16-byte loads need twice the depth to cover the same latency).
+    // Bytes in flight per thread.  A norm pass has one input stream where Adam has five, so each thread must keep more
+    // groups in flight to cover the loaded HBM latency: kDepth x (2 groups of 32 B for fp32 | 4 groups of 16 B for the
+    // 16-bit types).  MT_NORM_DEPTH=1|2 selects the depth for sweeps (profiles/r2_norm_depth_sweep.jsonl).
     constexpr int G = 8, THREADS = 256, MINB = 4;
+    static const int depth_knob = [] {
+        const char* e = getenv("MT_NORM_DEPTH");
+        const int v = e ? atoi(e) : 0;
+        return (v == 1 || v == 2) ? v : 2;
+    }();
     if (depth == 1) {
         MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
-            constexpr int U = sizeof(Tx) == 4 ? 2 : 4;
+            constexpr int U1 = sizeof(Tx) == 4 ? 2 : 4;
             if (mp) {
                 using Op = L2NormOp<Tx, true>;
                 typename Op::Params prm{out};
-                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+                rc = depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                                     : launch_table_kernel<Op, G, U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             } else {
                 using Op = L2NormOp<Tx, false>;
                 typename Op::Params prm{out};
-                rc = launch_table_kernel<Op, G, U, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
+                rc = depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                                     : launch_table_kernel<Op, G, U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             }
         })
     } else {

@@ -521,6 +521,26 @@ __device__ __forceinline__ void process_tile(const Op& op, char* const (&base)[O
     const int nvec = (t.len - h) / G;
     const int64_t v0 = t.start + h;
 
+    if constexpr (Op::kRawReduce) {
+        // One read-only list that is only reduced: keep the groups in flight as RAW words (4 registers per 16-bit
+        // group instead of 8 floats) and unpack at consumption, so that twice as many loads fit the register budget.
+        using T0 = ListT<Op, 0>;
+        constexpr int W = G * (int)sizeof(T0) / 4;
+        const T0* p0 = reinterpret_cast<const T0*>(base[0]) + v0;
+        for (int j0 = 0; j0 < nvec; j0 += THREADS * U) {
+            uint32_t w[U][W];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int j = j0 + u * THREADS + tid;
+                if (j < nvec) RawVec<W, true>::ld(p0 + (int64_t)j * G, w[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                const int j = j0 + u * THREADS + tid;
+                if (j < nvec) op.consume_raw(w[u], st);
+            }
+        }
+    } else
     for (int j0 = 0; j0 < nvec; j0 += THREADS * U) {
         float x[U][Op::kLists][G];
         if (j0 + THREADS * U <= nvec) {  // full round: all loads are issued before the first use
@@ -603,6 +623,7 @@ struct OpBase {
     __device__ __forceinline__ bool load(int) const { return true; }
     __device__ __forceinline__ bool store(int) const { return true; }
     static constexpr bool kTickets = false;  // finalizes inside the launch through DevTable::tickets (norm_tile_done)
+    static constexpr bool kRawReduce = false;  // single read-only list consumed through consume_raw() (process_tile)
     template <int THREADS, class S>
     __device__ __forceinline__ void end_tile_n(const DevTable&, const Tile&, uint32_t, S&, float*, int32_t*, bool) const {}
     template <class S> __device__ __forceinline__ void finish(S&, int32_t*) const {}

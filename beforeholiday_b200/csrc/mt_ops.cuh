@@ -360,6 +360,22 @@ template <class Tx, bool kMp = false> struct L2NormOp : OpBase {
     __device__ explicit L2NormOp(const Params& q) : p(q) {}
     __device__ __forceinline__ void init(State& s) const { s.sum = 0.f; }
     __device__ __forceinline__ void elem(float (&x)[1], State& s) const { s.sum = fadd(s.sum, fmul(x[0], x[0])); }
+    // vector path: groups stay packed while in flight and are unpacked here, in element order (same sum order as elem())
+    static constexpr bool kRawReduce = sizeof(Tx) <= 4;
+    template <int W> __device__ __forceinline__ void consume_raw(const uint32_t (&w)[W], State& s) const {
+#pragma unroll
+        for (int i = 0; i < W; i++) {
+            if constexpr (sizeof(Tx) == 4) {
+                const float x = __uint_as_float(w[i]);
+                s.sum = fadd(s.sum, fmul(x, x));
+            } else {
+                float lo, hi;
+                Packed16<Tx>::unpack(w[i], lo, hi);
+                s.sum = fadd(s.sum, fmul(lo, lo));
+                s.sum = fadd(s.sum, fmul(hi, hi));
+            }
+        }
+    }
     template <int THREADS>
     __device__ __forceinline__ void end_tile_n(const DevTable& tb, const Tile& t, uint32_t tile, State& s, float* smem,
                                                int32_t* noop, bool skipped) const {
