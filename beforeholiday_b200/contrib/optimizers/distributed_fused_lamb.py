@@ -305,7 +305,11 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         self._grads_generated.add(i)
         ready = [b for b in self._param_buckets[i] if not self._bucket_reduced[b]
                  and all(j in self._grads_generated for j in self._bucket_params[b])]
-        if ready:
+        if ready and self.rs_stream is None:        # no side stream (CPU stand-in): reduce in line
+            for b in ready:
+                self._reduce_scatter(b)
+                self._bucket_reduced[b] = True
+        elif ready:
             main = torch.cuda.current_stream(self.device)
             self.rs_stream.wait_stream(main)
             with torch.cuda.stream(self.rs_stream):

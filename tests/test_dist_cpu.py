@@ -192,7 +192,8 @@ def _lamb_cls():
     return CpuShardedLamb
 
 
-LAMB_OPTIONS = {"default": {}, "e5m2_allgather": {"e5m2_allgather": True}, "clip_before_ar": {"clip_after_ar": False}}
+LAMB_OPTIONS = {"default": {}, "e5m2_allgather": {"e5m2_allgather": True}, "clip_before_ar": {"clip_after_ar": False},
+                "overlap_hooks": {"overlap_reductions": True}}
 
 
 def _lamb_worker(rank, world, port, outdir, option="default"):
@@ -214,10 +215,18 @@ def _lamb_worker(rank, world, port, outdir, option="default"):
         opt.set_global_scale(64.0)
         order = params[0::2] + params[1::2]      # the optimizer's flat order
         for it in range(4):
-            for i, p in enumerate(order):
-                p.grad.copy_(make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape))
+            gs = [make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape)
+                  for i, p in enumerate(order)]
             if it == 2 and rank == 1:
-                order[3].grad.view(-1)[5] = float("inf")       # one rank overflows: every rank must skip the step
+                gs[3].view(-1)[5] = float("inf")               # one rank overflows: every rank must skip the step
+            if option == "overlap_hooks":
+                # a real backward pass (d/dp sum(p * g) = g): the hooks reduce-scatter each bucket as it fills up
+                opt.zero_grad()
+                sum((p * g).sum() for p, g in zip(order, gs)).backward()
+                assert any(opt._bucket_reduced)
+            else:
+                for p, g in zip(order, gs):
+                    p.grad.copy_(g)
             opt.complete_reductions()
             opt.step()
             assert int(opt._overflow_buf) == (1 if it == 2 else 0)
@@ -228,7 +237,8 @@ def _lamb_worker(rank, world, port, outdir, option="default"):
 
 
 @pytest.mark.timeout(300)
-@pytest.mark.parametrize("world,option", [(2, "default"), (4, "default"), (2, "e5m2_allgather"), (2, "clip_before_ar")])
+@pytest.mark.parametrize("world,option", [(2, "default"), (4, "default"), (2, "e5m2_allgather"), (2, "clip_before_ar"),
+                                          (2, "overlap_hooks")])
 def test_sharded_lamb_matches_single_process(tmp_path, world, option):
     import sys
 

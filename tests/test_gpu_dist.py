@@ -300,17 +300,26 @@ def _lamb_worker(rank, world, port, outdir, option="default"):
         init = [(torch.randn(n) * 0.05).bfloat16() for n in LAMB_SIZES]
         params = [torch.nn.Parameter(x.clone().to(dev)) for x in init]
         groups = [dict(params=params[0::2], weight_decay=0.01), dict(params=params[1::2], weight_decay=0.0)]
-        kw = {"default": {}, "e5m2_allgather": dict(e5m2_allgather=True), "clip_before_ar": dict(clip_after_ar=False)}[option]
+        kw = {"default": {}, "e5m2_allgather": dict(e5m2_allgather=True), "clip_before_ar": dict(clip_after_ar=False),
+              "overlap_hooks": dict(overlap_reductions=True)}[option]
         opt = DistributedFusedLAMB(groups, lr=2e-3, betas=(0.9, 0.999), eps=1e-6, max_grad_norm=1.0, dwu_num_blocks=2,
                                    dwu_num_chunks=2, **kw)
         opt.set_global_scale(64.0)
         order = params[0::2] + params[1::2]
         launches = []
         for it in range(4):
-            for i, p in enumerate(order):
-                p.grad.copy_(make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape))
+            gs = [make_grad(1000 * it + 10 * rank + i, p.numel(), torch.bfloat16, 64.0).view(p.shape).to(dev)
+                  for i, p in enumerate(order)]
             if it == 2 and rank == world - 1:
-                order[3].grad.view(-1)[5] = float("inf")
+                gs[3].view(-1)[5] = float("inf")
+            if option == "overlap_hooks":
+                # a real backward pass (d/dp sum(p * g) = g): the hooks reduce-scatter buckets on the side stream
+                opt.zero_grad()
+                sum((p * g).sum() for p, g in zip(order, gs)).backward()
+                assert any(opt._bucket_reduced)
+            else:
+                for p, g in zip(order, gs):
+                    p.grad.copy_(g)
             l0 = opt._amp_C().launch_count()
             opt.complete_reductions()
             opt.step()
@@ -325,7 +334,7 @@ def _lamb_worker(rank, world, port, outdir, option="default"):
 
 @pytest.mark.timeout(600)
 @pytest.mark.parametrize("world,option", [(2, "default"), (4, "default"), (2, "e5m2_allgather"), (2, "clip_before_ar"),
-                                          (4, "e5m2_allgather")])
+                                          (4, "e5m2_allgather"), (2, "overlap_hooks"), (4, "overlap_hooks")])
 def test_distributed_fused_lamb_matches_oracle_replay(tmp_path, world, option):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
