@@ -206,6 +206,9 @@ def run_distributed(args, rank, world, local_rank, device):
 
     # breakdown (each max over ranks)
     ms_update, _, _ = _timed(lambda: [opt._update_bucket(b, float(world)) for b in range(L.nbuckets)], args.steps, device)
+    # what a training loop still sees when the drop-in class has reduce-scattered the gradients during backward (hooks):
+    # update + all-gather pipeline only
+    ms_uag, _, _ = _timed(lambda: (opt.noop.zero_(), opt.update_and_gather(float(world))), max(2, args.steps // 2), device)
     ms_rs, _, _ = _timed(lambda: [opt._reduce_scatter(b) for b in range(L.nbuckets)], max(2, args.steps // 2), device)
     ms_ag, _, _ = _timed(lambda: [opt._all_gather(b) for b in range(L.nbuckets)], max(2, args.steps // 2), device)
     rs_s, ag_s = opt.rs_stream, opt.ag_stream
@@ -288,6 +291,7 @@ def run_distributed(args, rank, world, local_rank, device):
                              "step_fused_multicast": ms_mc, "step_fused_hybrid": ms_hy,
                              "hybrid_best_p2p_share": hybrid_best, "hybrid_search_ms": hybrid_search,
                              "step_nccl_serial": ms_serial, "update_only": ms_update,
+                             "update_and_gather_after_overlapped_grad_sync": ms_uag,
                              "reduce_scatter_only": ms_rs, "all_gather_only": ms_ag},
             "update_only": {"params_per_s_whole_job": P / (ms_update * 1e-3), "hbm_gbs_per_gpu": achieved},
             "nvlink": {"bytes_sent_per_gpu_per_collective": nvlink_bytes,

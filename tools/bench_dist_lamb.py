@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp16"])
+    ap.add_argument("--e5m2-allgather", action="store_true", help="parameters travel as one e5m2 byte each (reference option)")
+    ap.add_argument("--clip-before-ar", action="store_true", help="clip_after_ar=False (reference option)")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -50,7 +52,8 @@ def main():
         t.normal_(0, 0.02)
         params.append(torch.nn.Parameter(t))
     opt = DistributedFusedLAMB(params, lr=1e-4, betas=(0.9, 0.999), eps=1e-6, weight_decay=0.01, max_grad_norm=1.0,
-                               dwu_num_blocks=4, dwu_num_chunks=4)
+                               dwu_num_blocks=4, dwu_num_chunks=4, e5m2_allgather=args.e5m2_allgather,
+                               clip_after_ar=not args.clip_before_ar)
     del params
     opt.set_global_scale(torch.tensor([1024.0], device=dev))
     L = opt.layout
@@ -121,7 +124,8 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_ms, "scaling": "strong", "data": "synthetic",
             "config": {"workload": f"{args.workload}: DistributedFusedLAMB, {args.dtype} grads/params + fp32 p/m/v/u shards "
                                    f"({len(numels)} tensors, {P} params)", "nbuckets": L.nbuckets, "shard_elems": shard,
-                       "fragments_rank0": len(opt.frags)},
+                       "fragments_rank0": len(opt.frags), "e5m2_allgather": args.e5m2_allgather,
+                       "clip_after_ar": not args.clip_before_ar},
             "breakdown_ms": bd, "launches_per_step": launches,
             "kernel_hbm_gbs": {"stage1": 26 * shard / bd["stage1_only"] / 1e6, "stage2": 14 * shard / bd["stage2_only"] / 1e6,
                                "grad_norm": 2 * shard / bd["grad_norm_only"] / 1e6},
