@@ -24,9 +24,10 @@ gradient of the bucket has been produced (:325-362, 612-726).  What differs is u
   * `numels=[...]` (extension) instead of `params`: build the optimizer over bare sizes; parameters are created as
     views of the flat buffer.
 
-Not carried: `redundant_process_group` of size > 1 and a `distributed_process_group` different from `process_group`
-(a 2-D grid over several nodes) raise NotImplementedError; `pipeline_size` and `contiguous_grad_buffer` are accepted
-(the buffers here are always contiguous, the pipeline is the three-stream one of the engine).
+`process_group` may be a `distributed_process_group` x `redundant_process_group` grid as in the reference (:62-74): the
+state is sharded over the former and replicated over the latter; gradients are reduce-scattered over the shards'
+group, then all-reduced over the replicas' group (:717-732).  `pipeline_size` and `contiguous_grad_buffer` are
+accepted (the buffers here are always contiguous, the pipeline is the three-stream one of the engine).
 """
 from __future__ import annotations
 
@@ -62,17 +63,21 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                                f'(dtype={dtype}, grad_sync_dtype={grad_sync_dtype}, param_sync_dtype={param_sync_dtype}))')
         self.dtype, self.grad_sync_dtype, self.param_sync_dtype = dtype, grad_sync_dtype, param_sync_dtype
         self.device = torch.device(device)
+        # process_group = distributed_process_group x redundant_process_group (reference :62-74, :232-262): the state is
+        # sharded over the former and replicated over the latter
         self.process_group = process_group
-        if distributed_process_group is not None and distributed_process_group is not process_group:
-            raise NotImplementedError('DistributedFusedAdam: a distributed_process_group different from process_group '
-                                      '(multi-node 2-D grid) is not supported by this single-node build')
-        if redundant_process_group is not None and dist.get_world_size(redundant_process_group) > 1:
-            raise NotImplementedError('DistributedFusedAdam: redundant_process_group of size > 1 is not supported')
-        self.distributed_process_group = process_group
-        self.redundant_process_group = None
-        self.distributed_size = dist.get_world_size(process_group) if dist.is_initialized() else 1
-        self.distributed_rank = dist.get_rank(process_group) if dist.is_initialized() else 0
-        self.process_group_size, self.redundant_size = self.distributed_size, 1
+        self.distributed_process_group = process_group if distributed_process_group is None else distributed_process_group
+        self.redundant_process_group = redundant_process_group
+        inited = dist.is_initialized()
+        self.process_group_size = dist.get_world_size(process_group) if inited else 1
+        self.distributed_size = dist.get_world_size(self.distributed_process_group) if inited else 1
+        self.distributed_rank = dist.get_rank(self.distributed_process_group) if inited else 0
+        self.redundant_size = dist.get_world_size(redundant_process_group) if redundant_process_group is not None else 1
+        if self.process_group_size != self.distributed_size * self.redundant_size:
+            raise RuntimeError('Invalid process group configuration '
+                               f'(process group size = {self.process_group_size}, '
+                               f'distributed process group size = {self.distributed_size}, '
+                               f'redundant process group size = {self.redundant_size})')
         self.average_grad_sync = average_grad_sync
         self.overlap_grad_sync = overlap_grad_sync
         self.greedy_grad_copy = True
@@ -96,9 +101,11 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         # ---- engine: layout, flat buffers, fp32 shard state, collectives, kernels ------------------------------------------
         # bucket_cap_mb counts bytes of the gradient sync dtype, as in the reference (:262-270)
         self._eng = self._engine_cls(sizes, adam_w_mode=adam_w_mode, grad_dtype=grad_sync_dtype,
-                                     param_dtype=param_sync_dtype, process_group=process_group, device=self.device,
-                                     bucket_cap_mb=bucket_cap_mb, average_grad_sync=average_grad_sync, overlap=True,
-                                     fused_p2p=fused_p2p, groups=self.param_groups, group_of=group_of)
+                                     param_dtype=param_sync_dtype, process_group=self.distributed_process_group,
+                                     device=self.device, bucket_cap_mb=bucket_cap_mb,
+                                     average_grad_sync=average_grad_sync, overlap=True, fused_p2p=fused_p2p,
+                                     groups=self.param_groups, group_of=group_of,
+                                     redundant_group=redundant_process_group if self.redundant_size > 1 else None)
         E, L = self._eng, self._eng.layout
         self.bucket_size, self.shard_size = L.bucket_elems, L.sub_shard
         # buckets that hold a piece of parameter i: its flat range [o, o + n) cut at multiples of the bucket size
@@ -123,9 +130,9 @@ class DistributedFusedAdam(torch.optim.Optimizer):
                 if flat:
                     p.data = view.view(p.shape)
                 self._flat_param.append(flat)
-            if self.distributed_size > 1 and not created:
+            if self.process_group_size > 1 and not created:
                 # every rank starts from rank 0's values (the reference broadcasts parameter by parameter, :336-340)
-                E.broadcast_params()
+                self._broadcast_flat_params()
                 for i, p in enumerate(self._params):
                     if not self._flat_param[i]:
                         o, n = L.offsets[i], sizes[i]
@@ -149,6 +156,18 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         self._point_grads_at_flat_buffer()
         self._grad_accs = []
         self._register_post_backward_hooks()
+
+    def _broadcast_flat_params(self):
+        """Rank 0 of the WHOLE process group (all shards, all replicas) is the source."""
+        E = self._eng
+        if self.redundant_size == 1:
+            E.broadcast_params()
+        else:
+            src = 0 if self.process_group is None else dist.get_global_rank(self.process_group, 0)
+            buf = E.params_flat if E.params_flat.is_cuda else E.params_flat.float()
+            dist.broadcast(buf, src=src, group=self.process_group)
+            if buf is not E.params_flat:
+                E.params_flat.copy_(buf)
 
     # flat buffers and layout (bench.py and the tests fill gradients directly)
     @property
@@ -266,7 +285,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         cleared behind its reduce-scatter: a later micro-batch accumulates into the same buffer, and a second
         reduce-scatter must then add only NEW contributions to the owner's running sum."""
         E, L = self._eng, self._eng.layout
-        if self.distributed_size > 1:
+        if self.process_group_size > 1:
             E.reduce_gradients(buckets, side_stream=True)
             if during_backward:
                 ctx = torch.cuda.stream(E.rs_stream) if E.rs_stream is not None else contextlib.nullcontext()
@@ -360,8 +379,8 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         if not hasattr(self, "_norm_flag"):
             self._norm_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         sq = E.local_grad_sq(idx, flag=self._norm_flag)
-        if self.average_grad_sync and self.distributed_size > 1:
-            sq = sq / float(self.distributed_size) ** 2     # the buffer holds SUMS; the reference's holds averages
+        if self.average_grad_sync and self.process_group_size > 1:
+            sq = sq / float(self.process_group_size) ** 2   # the buffer holds SUMS; the reference's holds averages
         return sq.detach().view([])
 
     def grad_norm(self, parameters=(), norm_type=2.0, force=False):
@@ -423,7 +442,7 @@ class DistributedFusedAdam(torch.optim.Optimizer):
             return loss
 
         self.grad_sync()
-        world_div = float(self.distributed_size) if (self.average_grad_sync and self.distributed_size > 1) else 1.0
+        world_div = float(self.process_group_size) if (self.average_grad_sync and self.process_group_size > 1) else 1.0
         E.noop.zero_()
         if grad_scaler is not None:
             grad_norm = self.grad_norm()
@@ -487,8 +506,10 @@ class DistributedFusedAdam(torch.optim.Optimizer):
         if self.distributed_size == 1:
             return {'gathered_states': [mine]}
         gathered = [None] * self.distributed_size if self.distributed_rank == 0 else None
-        root = dist.get_global_rank(self.process_group, 0) if self.process_group is not None else 0
-        dist.gather_object(mine, gathered, dst=root, group=self.process_group)
+        # (with replicas every shard group gathers on its own first rank; the replicas' states are identical)
+        g = self.distributed_process_group
+        root = dist.get_global_rank(g, 0) if g is not None else 0
+        dist.gather_object(mine, gathered, dst=root, group=g)
         return {'gathered_states': gathered} if self.distributed_rank == 0 else None
 
     def load_state_dict(self, state_dict):

@@ -109,8 +109,13 @@ class FlatShardedAdam:
                  adam_w_mode=True, weight_decay=0.0, grad_dtype=torch.bfloat16, param_dtype=torch.bfloat16,
                  process_group=None, device=None, bucket_cap_mb: float = 1024.0, average_grad_sync=True, overlap=True,
                  per_param_weight_decay: Optional[Sequence[float]] = None, fused_p2p: bool = False,
-                 groups: Optional[List[dict]] = None, group_of: Optional[Sequence[int]] = None):
+                 groups: Optional[List[dict]] = None, group_of: Optional[Sequence[int]] = None, redundant_group=None):
         self.group = process_group
+        # optimizer state is SHARDED over `process_group` and REPLICATED over `redundant_group` (reference: a
+        # distributed_size x redundant_size grid, distributed_fused_adam.py:62-74); gradients are reduce-scattered over
+        # the former, then all-reduced over the latter (:717-732)
+        self.redundant_group = redundant_group
+        self.redundant_size = dist.get_world_size(redundant_group) if redundant_group is not None else 1
         self.world = dist.get_world_size(self.group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(self.group) if dist.is_initialized() else 0
         numels = [int(n) for n in numels]
@@ -119,7 +124,7 @@ class FlatShardedAdam:
         self.adam_w_mode = adam_w_mode
         self.average_grad_sync = average_grad_sync
         self.overlap = overlap
-        self.fused_p2p = bool(fused_p2p) and self.world > 1
+        self.fused_p2p = bool(fused_p2p) and self.world > 1 and self.redundant_size == 1
         # fused multicast route: sixteenths of the flat buffer whose gradient loads / parameter stores go peer-to-peer
         # instead of through the switch (0, 0 = everything through the switch); see DistAdamP2POp in csrc/mt_ops.cuh
         self.hybrid_split = (0, 0)
@@ -264,6 +269,12 @@ class FlatShardedAdam:
         if self.world > 1:
             dist.all_gather_into_tensor(self.params_flat[lo:hi], self.params_flat[olo:ohi], group=self.ag_group)
 
+    def _reduce_redundant(self, b: int):
+        """Sum the owned sub-shard over the replicas of this shard (no-op without a redundant group)."""
+        if self.redundant_size > 1:
+            olo, ohi = self.layout.owned_range(b)
+            dist.all_reduce(self.grads_flat[olo:ohi], op=dist.ReduceOp.SUM, group=self.redundant_group)
+
     def _all_reduce_scalar(self, t, op):
         if self.world > 1:
             dist.all_reduce(t, op=op, group=self.group)
@@ -402,12 +413,14 @@ class FlatShardedAdam:
         if self.rs_stream is None or not side_stream:
             for b in buckets:
                 self._reduce_scatter(b)
+                self._reduce_redundant(b)
             return
         main = torch.cuda.current_stream(self.device)
         self.rs_stream.wait_stream(main)
         with torch.cuda.stream(self.rs_stream):
             for b in buckets:
                 self._reduce_scatter(b)
+                self._reduce_redundant(b)
                 e = torch.cuda.Event()
                 e.record(self.rs_stream)
                 self._rs_events[b] = e
@@ -465,7 +478,7 @@ class FlatShardedAdam:
         only."""
         self.step_count += 1
         self.noop.zero_()
-        scale = grad_scale * (self.world if (self.average_grad_sync and not grads_already_reduced) else 1)
+        scale = grad_scale * (self.world * self.redundant_size if (self.average_grad_sync and not grads_already_reduced) else 1)
         if max_grad_norm is not None:
             assert not grads_already_reduced
             return self._step_clipped(scale, float(max_grad_norm))

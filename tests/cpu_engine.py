@@ -24,6 +24,13 @@ class CpuShardedAdam(FlatShardedAdam):
         olo, ohi = self.layout.owned_range(b)
         self.grads_flat[olo:ohi].copy_(buf[olo - lo:ohi - lo])  # only the owned sub-shard is defined afterwards
 
+    def _reduce_redundant(self, b):
+        if self.redundant_size > 1:
+            olo, ohi = self.layout.owned_range(b)
+            buf = self.grads_flat[olo:ohi].float()
+            dist.all_reduce(buf, group=self.redundant_group)
+            self.grads_flat[olo:ohi].copy_(buf)
+
     def _all_gather(self, b):
         if self.world == 1:
             return

@@ -244,6 +244,27 @@ def overflow_does_not_stick(make, rank, device):
     return {}
 
 
+def grid_2x2(make, rank, device):
+    """A distributed x redundant process-group grid (reference constructor :62-74, :232-262; gradient path :717-732):
+    world 4 as two replicas of a state sharded over two ranks.  Every rank must end with the same parameters as
+    AdamW on the gradients averaged over all four.  (Other world sizes: nothing to do.)"""
+    if dist.get_world_size() != 4:
+        return {}
+    shard_groups = [dist.new_group([0, 1]), dist.new_group([2, 3])]
+    replica_groups = [dist.new_group([0, 2]), dist.new_group([1, 3])]
+    out = matches_pytorch(make, rank, device, distributed_process_group=shard_groups[rank // 2],
+                          redundant_process_group=replica_groups[rank % 2])
+    # and the grouping is checked, as in the reference
+    try:
+        make([torch.nn.Parameter(torch.zeros(4, device=device))], distributed_process_group=shard_groups[rank // 2],
+             device=device)
+    except RuntimeError as e:
+        assert "Invalid process group configuration" in str(e)
+    else:
+        raise AssertionError("a 2-rank shard group without replicas inside a 4-rank process group must be refused")
+    return out
+
+
 CASES = {
     "matches_pytorch": matches_pytorch,
     "matches_pytorch_no_overlap": lambda make, rank, device, **kw: matches_pytorch(
@@ -261,4 +282,5 @@ CASES = {
     "grad_scaler": grad_scaler,
     "checkpoint": checkpoint,
     "overflow_does_not_stick": overflow_does_not_stick,
+    "grid_2x2": grid_2x2,
 }

@@ -1,5 +1,5 @@
 """The reference's DistributedFusedAdam test scenarios (apex/contrib/test/optimizers/test_dist_adam.py) against this
-repo's drop-in class, on CPU: world 2 (and 3, an odd size) over gloo, with the oracle standing in for the CUDA update
+repo's drop-in class, on CPU: world 2, 3 (an odd size) and 4 (which also runs the 2 x 2 shard / replica grid) over gloo, with the oracle standing in for the CUDA update
 (tests/cpu_engine.py).  What is under test is the optimizer's host logic: flat layout, param groups with their own lr,
 post-backward hooks and bucket bookkeeping across micro-batches / no_sync, clip_grad_norm, the GradScaler protocol with
 device-side skip, gather-on-root checkpointing.  The GPU twin (NCCL, real kernels) is tests/test_gpu_dist_adam.py."""
@@ -72,7 +72,7 @@ def _results(world, tmp_path_factory):
 
 
 @pytest.mark.timeout(900)
-@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("world", [2, 3, 4])
 @pytest.mark.parametrize("case", list(CASES))
 def test_dist_adam_reference_scenarios_cpu(case, world, tmp_path_factory):
     res = _results(world, tmp_path_factory)
