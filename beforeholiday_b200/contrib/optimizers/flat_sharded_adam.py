@@ -360,7 +360,9 @@ class FlatShardedAdam:
         self.step_count += 1
         self.noop.zero_()
         scale = grad_scale * (self.world if self.average_grad_sync else 1)
-        use_mc = self.has_multicast if multicast is None else (bool(multicast) and self.has_multicast)
+        # default route: through the switch from 4 ranks on; at 2 ranks plain peer access moves S/2 per direction where
+        # the switch moves 1.5 S (it also reads / writes the requester's own copy) -- 23.9 vs 40.0 ms on Llama-3-8B
+        use_mc = (self.has_multicast and self.world > 2) if multicast is None else (bool(multicast) and self.has_multicast)
         self._hdl_g.barrier(channel=0)
         for e in self._group_launch_sets():
             self._refresh_hp(e)
