@@ -339,3 +339,39 @@ def test_sharded_adam_on_a_real_module_world2_vs_adamw(tmp_path, clip):
         assert torch.equal(a, b)
     for a, b in zip(res[0]["mine"], res[0]["ref"]):
         assert torch.allclose(a, b, rtol=2e-5, atol=2e-6)
+
+
+def test_dropin_over_bare_sizes_matches_the_engine():
+    """`numels=` (extension): the optimizer creates its parameters as views of the flat buffer.  One process, no process
+    group: two steps on gradients written straight into the flat buffer must equal the engine's result bit for bit."""
+    sizes = [1000, 7, 4096, 333]
+    torch.manual_seed(3)
+    init = torch.randn(sum(sizes)) * 0.02
+    grads = [torch.randn(sum(sizes)) * 1e-2 for _ in range(2)]
+    kw = dict(lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.1)
+
+    def fill(flat, layout, src):
+        o = 0
+        for n, off in zip(sizes, layout.offsets):
+            flat[off:off + n].copy_(src[o:o + n])
+            o += n
+
+    opt = CpuDistributedFusedAdam(numels=sizes, device="cpu", bucket_cap_mb=4096 * 4 / 2 ** 20, **kw)
+    assert [p.numel() for g in opt.param_groups for p in g["params"]] == sizes
+    assert all(p.data_ptr() == opt.params_flat.data_ptr() + 4 * o
+               for p, o in zip((p for g in opt.param_groups for p in g["params"]), opt.layout.offsets))
+    eng = CpuShardedAdam(sizes, device="cpu", grad_dtype=torch.float32, param_dtype=torch.float32,
+                         bucket_cap_mb=4096 * 4 / 2 ** 20, **kw)
+    for o in (opt, eng):
+        fill(o.params_flat, o.layout, init)
+    opt._init_masters()
+    eng.init_master_from_params()
+    for g in grads:
+        opt.zero_grad()
+        eng.zero_grad()
+        fill(opt.grads_flat, opt.layout, g)
+        fill(eng.grads_flat, eng.layout, g)
+        opt.step()
+        eng.step()
+    assert torch.equal(opt.params_flat, eng.params_flat) and not torch.equal(opt.params_flat[:1000], init[:1000])
+    assert opt.state_dict(gather_on_root=False)["state"]["step"] == 2
