@@ -107,24 +107,30 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
     // Bytes in flight per thread.  A norm pass has one input stream where Adam has five, so each thread must keep more
     // groups in flight to cover the loaded HBM latency: kDepth x (2 groups of 32 B for fp32 | 4 groups of 16 B for the
     // 16-bit types).  MT_NORM_DEPTH=1|2 selects the depth for sweeps (profiles/r2_norm_depth_sweep.jsonl).
+    // MT_NORM_DEPTH=3 additionally widens the 16-bit accesses to 32 bytes (16 elements per load, LDG.256): measured equal
+    // to depth 2 (49.2 vs 48.7 us on GPT-2's 249 MB of fp16 gradients) -- at that size the pass is at what a plain copy
+    // of the same bytes attains (49.9 us), so depth 2 stays the default and 3 a knob.
     constexpr int G = 8, THREADS = 256, MINB = 4;
     static const int depth_knob = [] {
         const char* e = getenv("MT_NORM_DEPTH");
         const int v = e ? atoi(e) : 0;
-        return (v == 1 || v == 2) ? v : 2;
+        return (v >= 1 && v <= 3) ? v : 2;
     }();
     if (depth == 1) {
         MT_DISPATCH_FHB(tl->dtype[0], Tx, who, {
             constexpr int U1 = sizeof(Tx) == 4 ? 2 : 4;
+            constexpr int GW = sizeof(Tx) == 4 ? 8 : 16;   // wide variant: 32-byte accesses for every dtype
             if (mp) {
                 using Op = L2NormOp<Tx, true>;
                 typename Op::Params prm{out};
-                rc = depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                rc = depth_knob == 3 ? launch_table_kernel<Op, GW, 4, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                   : depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
                                      : launch_table_kernel<Op, G, U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             } else {
                 using Op = L2NormOp<Tx, false>;
                 typename Op::Params prm{out};
-                rc = depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                rc = depth_knob == 3 ? launch_table_kernel<Op, GW, 4, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
+                   : depth_knob == 2 ? launch_table_kernel<Op, G, 2 * U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream)
                                      : launch_table_kernel<Op, G, U1, THREADS, MINB>(tb, prm, noop_flag, tl->device, stream);
             }
         })
