@@ -147,6 +147,13 @@ static int norm_common(const char* who, int chunk_size, int32_t* noop_flag, cons
 
 }  // namespace mt
 
+#ifdef MT_TRACE
+extern "C" int mt_debug_set_trace(void* buf) {  // tools/norm_trace.py; not part of the product ABI
+    unsigned long long* p = static_cast<unsigned long long*>(buf);
+    return (int)cudaMemcpyToSymbol(mt::g_mt_trace, &p, sizeof(p));
+}
+#endif
+
 extern "C" size_t mt_norm_scratch_bytes(int chunk_size, const MtTensorLists* tl) {
     if (!tl || !tl->numel || chunk_size <= 0) return 0;
     return (size_t)mt::count_tiles(tl, chunk_size / mt::norm_tiles_per_chunk(chunk_size)) * sizeof(float);

@@ -333,10 +333,18 @@ __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t
     const bool per_tensor = o.ret_pt != nullptr || o.sub > 1;
     if (tid == 0) {
         unsigned r = 0;
-        __threadfence();  // this tile's partials (and flag) before its tickets
+        uint32_t b = 0, e = 0;
         if (per_tensor) {
-            const uint32_t b = __ldg(tb.tile_begin + t.tensor), e = __ldg(tb.tile_begin + t.tensor + 1);
-            if (atomicAdd(tb.tickets + t.tensor, 1u) + 1u == e - b) r |= 1u;
+            b = __ldg(tb.tile_begin + t.tensor);
+            e = __ldg(tb.tile_begin + t.tensor + 1);
+        }
+        __threadfence();  // this tile's partials (and flag) before its tickets
+        // both tickets go out before either answer is looked at: one round trip to L2 instead of two
+        unsigned tk = 0, gk = 0;
+        if (per_tensor) tk = atomicAdd(tb.tickets + t.tensor, 1u);
+        if (o.ret_global) gk = atomicAdd(tb.tickets + tb.ntensors, 1u);
+        if (per_tensor) {
+            if (tk + 1u == e - b) r |= 1u;
             const bool quiet = kQuietWhenFlagged && *reinterpret_cast<const volatile int32_t*>(noop) != 0;
             if (o.ret_pt && !quiet) {
                 if (t.start == 0)
@@ -347,8 +355,7 @@ __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t
                         for (int s = 0; s < NSETS; s++) o.ret_pt[(size_t)s * tb.ntensors + k] = 0.f;
             }
         }
-        if (o.ret_global)
-            if (atomicAdd(tb.tickets + tb.ntensors, 1u) + 1u == tb.ntiles) r |= 2u;
+        if (o.ret_global && gk + 1u == tb.ntiles) r |= 2u;
         if (r) __threadfence();  // everybody else's partials after the last ticket
         *sflag = r;
     }
@@ -365,12 +372,24 @@ __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t
         for (int s = 0; s < NSETS; s++) {
             const float* p = o.partials + (size_t)s * tb.ntiles;
             float acc = 0.f;
-            for (uint32_t c = lane; c < nchunks; c += 32) {
-                const uint32_t i0 = b + c * sub, i1 = min(i0 + sub, e);
-                float cs = __ldcg(p + i0);
-                for (uint32_t i = i0 + 1; i < i1; i++) cs = fadd(cs, __ldcg(p + i));
-                bad = bad || !finite_f(cs);
-                acc = fadd(acc, cs);
+            if (sub == 1) {
+                // four tiles per lane and trip: the loads go out together, the additions keep the lane's tile order
+                for (uint32_t c0 = lane; c0 < nchunks; c0 += 4 * 32) {
+                    float cs[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) cs[k] = c0 + 32 * k < nchunks ? __ldcg(p + b + c0 + 32 * k) : 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; k++)
+                        if (c0 + 32 * k < nchunks) acc = fadd(acc, cs[k]);
+                }
+            } else {
+                for (uint32_t c = lane; c < nchunks; c += 32) {
+                    const uint32_t i0 = b + c * sub, i1 = min(i0 + sub, e);
+                    float cs = __ldcg(p + i0);
+                    for (uint32_t i = i0 + 1; i < i1; i++) cs = fadd(cs, __ldcg(p + i));
+                    bad = bad || !finite_f(cs);
+                    acc = fadd(acc, cs);
+                }
             }
 #pragma unroll
             for (int k = 16; k > 0; k >>= 1) acc = fadd(acc, __shfl_xor_sync(0xffffffffu, acc, k));
@@ -384,8 +403,23 @@ __device__ __forceinline__ void norm_tile_done(const DevTable& tb, const Tile& t
         for (int s = 0; s < NSETS; s++) {
             const float* p = o.partials + (size_t)s * tb.ntiles;
             float a0 = 0.f, a1 = 0.f;  // virtual threads tid and tid + 256 of a 512-thread block
-            for (uint32_t i = tid; i < tb.ntiles; i += 512) a0 = fadd(a0, __ldcg(p + i));
-            for (uint32_t i = tid + 256; i < tb.ntiles; i += 512) a1 = fadd(a1, __ldcg(p + i));
+            // eight loads per trip go out together (this runs once, at the very end of the launch, with nothing
+            // else left to hide its latency); each accumulator still adds its partials in increasing order
+            for (uint32_t i0 = tid; i0 < tb.ntiles; i0 += 4 * 512) {
+                float x[4], y[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t i = i0 + 512 * k;
+                    x[k] = i < tb.ntiles ? __ldcg(p + i) : 0.f;
+                    y[k] = i + 256 < tb.ntiles ? __ldcg(p + i + 256) : 0.f;
+                }
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t i = i0 + 512 * k;
+                    if (i < tb.ntiles) a0 = fadd(a0, x[k]);
+                    if (i + 256 < tb.ntiles) a1 = fadd(a1, y[k]);
+                }
+            }
 #pragma unroll
             for (int k = 16; k > 0; k >>= 1) {
                 a0 = fadd(a0, __shfl_xor_sync(0xffffffffu, a0, k));
@@ -581,6 +615,23 @@ __device__ __forceinline__ void fetch_bases(const DevTable& tb, int tensor, char
      ...);
 }
 
+#ifdef MT_TRACE
+// Debug builds only (tools/norm_trace.py): per-CTA globaltimer stamps {entry, tile located, tile streamed, tile handed
+// in, SM id} written by thread 0.  One copy per translation unit; the setter lives beside the kernels it traces.
+static __device__ unsigned long long* g_mt_trace = nullptr;
+__device__ __forceinline__ unsigned long long mt_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void mt_stamp(int slot) {
+    if (threadIdx.x == 0 && g_mt_trace) g_mt_trace[(size_t)blockIdx.x * 8 + slot] = mt_now();
+}
+#define MT_STAMP(slot) mt_stamp(slot)
+#else
+#define MT_STAMP(slot)
+#endif
+
 // The table-driven kernel.  grid = ntiles (one CTA per tile); the loop only matters when the grid is capped.
 template <class Op, int G, int U, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
@@ -599,16 +650,27 @@ mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __res
     typename Op::State st;
     op.init(st);
     using Seq = std::make_integer_sequence<int, Op::kLists>;
+    MT_STAMP(0);
     for (uint32_t tile = blockIdx.x; tile < tb.ntiles; tile += gridDim.x) {
         const Tile t = locate_tile(tb, tile);
         if (!skipped) {
             char* base[Op::kLists];
             fetch_bases<Op>(tb, t.tensor, base, Seq{});
             op.begin_tensor(t.tensor);
+            MT_STAMP(1);
             process_tile<Op, G, U, THREADS>(op, base, t, st);
+            MT_STAMP(2);
         }
         op.template end_tile_n<THREADS>(tb, t, tile, st, smem, noop, skipped);
+        MT_STAMP(3);
     }
+#ifdef MT_TRACE
+    if (threadIdx.x == 0 && g_mt_trace) {
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        g_mt_trace[(size_t)blockIdx.x * 8 + 4] = smid;
+    }
+#endif
     op.finish(st, noop);
 }
 
