@@ -368,6 +368,9 @@ def main():
 
             line["configs"] = run_configs(amp_C, device, max(10, args.steps), args.warmup, peak, sampler,
                                           ClockSampler.summarize, log, with_ref=not args.no_refcuda)
+            line["configs_l2"] = ("before every timed step, outside its event pair: 256 MiB written, then 256 MiB of a "
+                                  "second buffer read (L2 left full of clean foreign lines; a write-only flush makes the "
+                                  "timed pass pay for the flush's write-backs -- ms_after_write_only_flush)")
         except Exception as e:  # noqa: BLE001
             log("[bench] configs leg failed:", repr(e))
             line["configs"] = {"error": repr(e)[:300]}

@@ -2,8 +2,12 @@
 timed the same way as the headline C5 step and reported inside the same JSON line under "configs".
 
 Per config: W >= 3 warm-up steps, then rounds of K steps; every step sits between its own pair of CUDA events on the
-launching stream, with an L2 flush (a 256 MiB write, outside the event pair) before it, so small working sets (C1 fits
-L2 many times over) are measured from HBM like the large ones.  Rounds repeat until the config has run for ~0.4 s so
+launching stream, with an L2 flush (outside the event pair) before it, so small working sets (C1 fits L2 many times
+over) are measured from HBM like the large ones.  The flush is a 256 MiB write FOLLOWED BY a 256 MiB read of a second
+buffer: a write alone leaves L2 full of dirty lines, and the timed pass then pays for writing them back (126 MB of
+DRAM writes that are not its own: +3.4 us on the 249 MB norm pass, +15.5 us on the 498 MB one, tools/norm_trace.py
+--clean-flush / profiles/r2_norm_trace_flush_modes.txt); after the read pass L2 holds clean lines of a foreign buffer.
+Passes under 2 GB also report `ms_after_write_only_flush` for comparison with earlier records.  Rounds repeat until the config has run for ~0.4 s so
 that the nvidia-smi sampler sees it; `ms` is the median over rounds of the per-round mean step time.  `gbs` =
 bytes_per_param x params / ms with SURVEY 8(d)'s algorithmic bytes; `frac` = gbs / MEASURED_PEAKS hbm_gbs.  Passes that
 move less than 2 GB also carry `copy_same_bytes_ms`: a plain `dst.copy_(src)` of the same total bytes under the same
@@ -43,9 +47,10 @@ class _Timer:
     def __init__(self, device, steps, warmup, sampler, summarize):
         self.device, self.steps, self.warmup = device, steps, max(3, warmup)
         self.flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=device)
+        self.flush_read = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=device)
         self.sampler, self.summarize = sampler, summarize
 
-    def __call__(self, fn, min_wall_s=0.45, max_rounds=100000):
+    def __call__(self, fn, min_wall_s=0.45, max_rounds=100000, write_only_flush=False):
         """-> (gpu ms per step, host enqueue ms per step, clocks record)."""
         for _ in range(self.warmup):
             fn()
@@ -57,6 +62,8 @@ class _Timer:
             h = 0.0
             for _ in range(self.steps):
                 self.flush.zero_()
+                if not write_only_flush:
+                    self.flush_read.sum()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a.record()
                 s = time.perf_counter()
@@ -119,6 +126,7 @@ def run_configs(amp_C, device, steps, warmup, peak, sampler, summarize, log, wan
             cms, _, _, _ = timer(lambda: dst.copy_(src), min_wall_s=0.15)
             d["copy_same_bytes_ms"] = cms
             d["frac_of_copy_same_bytes"] = cms / ms
+            d["ms_after_write_only_flush"] = timer(fn, min_wall_s=0.15, write_only_flush=True)[0]
             del src, dst
         if extra:
             d.update(extra)

@@ -42,6 +42,10 @@ def main():
     ap.add_argument("--dtype", default="fp16", choices=["fp16", "fp32"])
     ap.add_argument("--per-tensor", type=int, default=0)
     ap.add_argument("--build-only", action="store_true")
+    ap.add_argument("--no-flush", action="store_true", help="leave L2 as the previous launch left it")
+    ap.add_argument("--clean-flush", action="store_true",
+                    help="after writing the flush buffer, READ a second one: L2 is left full of clean lines, so the "
+                         "traced launch does not pay for writing the flush's dirty lines back")
     args = ap.parse_args()
     so = build()
     if args.build_only:
@@ -62,6 +66,7 @@ def main():
     ret_pt = torch.zeros(len(xs), dtype=torch.float32, device=dev)
     trace = torch.zeros(ntiles * 8, dtype=torch.int64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush2 = torch.zeros(64 << 20, dtype=torch.float32, device=dev)
     stream = _lib.stream_ptr(dev)
 
     def call():
@@ -74,7 +79,10 @@ def main():
     assert L.mt_debug_set_trace(_lib.vp(trace)) == 0
     runs = []
     for _ in range(3):
-        flush.zero_()
+        if not args.no_flush:
+            flush.zero_()
+            if args.clean_flush:
+                flush2.sum()
         trace.zero_()
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -113,7 +121,7 @@ def main():
             "ctas_streaming_per_us": active, "ctas_resident_per_us": resident,
             "sms_used": int(len(set(t[:, 4].tolist()))),
         })
-    print(json.dumps({"dtype": args.dtype, "per_tensor": args.per_tensor, "bytes": sum(numels) * xs[0].element_size(),
+    print(json.dumps({"dtype": args.dtype, "per_tensor": args.per_tensor, "l2_flushed": not args.no_flush, "clean_flush": args.clean_flush, "bytes": sum(numels) * xs[0].element_size(),
                       "runs": runs}))
 
 
