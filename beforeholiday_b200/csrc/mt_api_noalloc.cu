@@ -130,6 +130,7 @@ extern "C" int mt_multi_tensor_l2norm_noalloc(int chunk_size, int32_t* noop_flag
     MT_CUDA_OK(cudaMemsetAsync(dev + kTicketOff, 0, (nt + 1) * 4, stream));  // the counters must start at zero
 
     DevTable tb;
+    tb.inl = 0;
     tb.tile_begin = reinterpret_cast<const uint32_t*>(dev);
     tb.numel = reinterpret_cast<const int64_t*>(dev + off_numel);
     tb.ptrs = reinterpret_cast<const void* const*>(dev + off_ptrs);

@@ -36,6 +36,15 @@ struct DevTable {
     // [ntensors + 1] completion counters of the reducing ops (per tensor; [ntensors] = whole launch).  Zero between
     // launches: the CTA that takes the last ticket finalizes and puts the counter back to zero (norm_tile_done below).
     uint32_t* tickets;
+    // Small tables (<= kInlineTensors tensors, <= kInlineLists lists) travel in the kernel arguments as well: the lookup
+    // at the head of every CTA then reads the parameter bank instead of chasing two or three dependent global loads
+    // (cold after anything that swept L2), which is most of what a launch over a few small tensors costs beyond its
+    // bytes (C1: 6 tensors, 27.6 MB).  `inl` = 0: the arrays below are unset, use the device blob.
+    static constexpr int kInlineTensors = 8, kInlineLists = 5;
+    int32_t inl;
+    uint32_t inl_tile_begin[kInlineTensors + 1];
+    int64_t inl_numel[kInlineTensors];
+    const void* inl_ptrs[kInlineLists][kInlineTensors];
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -253,6 +262,7 @@ struct Tile {
     int64_t start;  // element offset inside the tensor
 };
 
+template <bool kInline = true>
 __device__ __forceinline__ Tile locate_tile(const DevTable& tb, uint32_t tile) {
     // upper_bound(tile_begin, tile) - 1 : last tensor whose first tile is <= tile.  Empty tensors have
     // tile_begin[t] == tile_begin[t+1] and are skipped naturally.
@@ -260,6 +270,18 @@ __device__ __forceinline__ Tile locate_tile(const DevTable& tb, uint32_t tile) {
     // loads and 50 000 take 4 (a bisection: 9 and 16).  That latency sits at the head of every CTA; it is hidden while
     // other CTAs of the SM stream, but not at the start of a launch, which is what a 40-microsecond norm pass feels.
     // Called with the whole CTA converged (the tile index is uniform), every warp searching redundantly.
+    if (kInline && tb.inl) {  // uniform: the table came with the kernel arguments
+        int lo = 0;
+#pragma unroll
+        for (int k = 1; k < DevTable::kInlineTensors; k++)
+            if (k < tb.ntensors && tb.inl_tile_begin[k] <= tile) lo = k;
+        Tile t;
+        t.tensor = lo;
+        t.start = (int64_t)(tile - tb.inl_tile_begin[lo]) * tb.tile_elems;
+        const int64_t rem = tb.inl_numel[lo] - t.start;
+        t.len = rem < tb.tile_elems ? (int32_t)rem : tb.tile_elems;
+        return t;
+    }
     int lo = 0, hi = tb.ntensors;  // invariant: tile_begin[lo] <= tile < tile_begin[hi]
     const int lane = threadIdx.x & 31;
     while (hi - lo > 1) {
@@ -611,6 +633,12 @@ __device__ __forceinline__ void process_tile(const Op& op, char* const (&base)[O
 template <class Op, int... Ds>
 __device__ __forceinline__ void fetch_bases(const DevTable& tb, int tensor, char* (&base)[Op::kLists],
                                             std::integer_sequence<int, Ds...>) {
+    if constexpr (Op::kInlineTable && Op::kLists <= DevTable::kInlineLists) {
+        if (tb.inl) {
+            ((base[Ds] = (char*)tb.inl_ptrs[Ds][tensor]), ...);
+            return;
+        }
+    }
     ((base[Ds] = (char*)__ldg(reinterpret_cast<const unsigned long long*>(tb.ptrs) + (size_t)Ds * tb.ntensors + tensor)),
      ...);
 }
@@ -652,7 +680,7 @@ mt_table_kernel(const DevTable tb, const typename Op::Params prm, int32_t* __res
     using Seq = std::make_integer_sequence<int, Op::kLists>;
     MT_STAMP(0);
     for (uint32_t tile = blockIdx.x; tile < tb.ntiles; tile += gridDim.x) {
-        const Tile t = locate_tile(tb, tile);
+        const Tile t = locate_tile<Op::kInlineTable>(tb, tile);
         if (!skipped) {
             char* base[Op::kLists];
             fetch_bases<Op>(tb, t.tensor, base, Seq{});
@@ -686,6 +714,10 @@ struct OpBase {
     __device__ __forceinline__ bool store(int) const { return true; }
     static constexpr bool kTickets = false;  // finalizes inside the launch through DevTable::tickets (norm_tile_done)
     static constexpr bool kRawReduce = false;  // single read-only list consumed through consume_raw() (process_tile)
+    // Small tables are read from the kernel arguments (DevTable::inl).  The sharded-update ops opt out: their launches
+    // are never small, and the second lookup path costs them registers they do not have (hot-loop spills under the
+    // 64-register cap, tools/sass_summary.py).
+    static constexpr bool kInlineTable = true;
     template <int THREADS, class S>
     __device__ __forceinline__ void end_tile_n(const DevTable&, const Tile&, uint32_t, S&, float*, int32_t*, bool) const {}
     template <class S> __device__ __forceinline__ void finish(S&, int32_t*) const {}

@@ -99,6 +99,7 @@ template <class Tp, int kMode> struct AdamOp : OpBase {
 // DistAdamFunctor: apex/contrib/csrc/optimizers/multi_tensor_distopt_adam_kernel.cu:52-63,103-116.
 // lists: p, m, v (fp32), g (Tg) [, p_copy (Tg)].  Per-tensor hyper-parameters live in device arrays.
 template <class Tg, bool kCopy, bool kHonourNoop> struct DistAdamOp : OpBase {
+    static constexpr bool kInlineTable = false;  // shard updates are never small launches (OpBase)
     static constexpr int kLists = kCopy ? 5 : 4;
     template <int D> using T = typename Types<float, float, float, Tg, Tg>::template at<D>;
     static constexpr unsigned kRead = 0b01111, kWrite = kCopy ? 0b10111 : 0b00111;

@@ -340,9 +340,21 @@ int acquire_locked(DeviceCache& c, Entry* e, cudaStream_t stream, bool capturing
     return MT_OK;
 }
 
-inline void fill_out(Entry* e, int device, cudaStream_t stream, int slot, size_t nt, int tile_elems, size_t off_tb,
-                     size_t off_numel, size_t off_ptrs, TableRef* out) {
+inline void fill_out(Entry* e, int device, cudaStream_t stream, int slot, size_t nt, int depth, int tile_elems,
+                     size_t off_tb, size_t off_numel, size_t off_ptrs, TableRef* out) {
     const uint8_t* d = static_cast<const uint8_t*>(e->dev);
+    out->inl = 0;
+    if (nt <= (size_t)DevTable::kInlineTensors && depth <= DevTable::kInlineLists) {
+        // small table: a copy rides in the kernel arguments (DevTable::inl), taken from the entry's exact host blob
+        const uint8_t* h = e->host.data();
+        out->inl = 1;
+        memset(out->inl_tile_begin, 0, sizeof(out->inl_tile_begin));
+        memset(out->inl_numel, 0, sizeof(out->inl_numel));
+        memset(out->inl_ptrs, 0, sizeof(out->inl_ptrs));
+        memcpy(out->inl_tile_begin, h + off_tb, (nt + 1) * 4);
+        memcpy(out->inl_numel, h + off_numel, nt * 8);
+        for (int l = 0; l < depth; l++) memcpy(out->inl_ptrs[l], h + off_ptrs + (size_t)l * nt * 8, nt * 8);
+    }
     out->tile_begin = reinterpret_cast<const uint32_t*>(d + off_tb);
     out->numel = reinterpret_cast<const int64_t*>(d + off_numel);
     out->ptrs = reinterpret_cast<const void* const*>(d + off_ptrs);
@@ -408,7 +420,7 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, Tabl
             const int rc = acquire_locked(c, e, stream, capturing, &slot);
             if (rc) return rc;
             if (i) mru_touch(c, e);
-            fill_out(e, device, stream, slot, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
+            fill_out(e, device, stream, slot, nt, depth, tile_elems, off_tb, off_numel, off_ptrs, out);
             return MT_OK;
         }
     }
@@ -504,7 +516,7 @@ int get_table(const MtTensorLists* tl, int tile_elems, cudaStream_t stream, Tabl
     const int rc = acquire_locked(c, e, stream, capturing, &slot);
     if (rc) return rc;
     mru_touch(c, e);
-    fill_out(e, device, stream, slot, nt, tile_elems, off_tb, off_numel, off_ptrs, out);
+    fill_out(e, device, stream, slot, nt, depth, tile_elems, off_tb, off_numel, off_ptrs, out);
     return MT_OK;
 }
 

@@ -205,3 +205,48 @@ def test_apply_flat_dist_call_writes_back_into_non_default_layouts():
     for t, w in zip((a, b, c, d), want):
         assert torch.equal(t, w)
     assert a.is_contiguous(memory_format=torch.channels_last)
+
+
+# ------------------------------------------------------------------------------------------------ small tables
+@pytest.mark.parametrize("n", [1, 7, 8, 9])
+def test_small_table_in_kernel_arguments_matches_device_table(amp_C, n):
+    """Tables of up to 8 tensors ride in the kernel arguments (DevTable::inl, csrc/mt_common.cuh); larger ones are read
+    from the device blob.  The same tensors processed as one call of n tensors and as part of a call of n + 8 tensors
+    (always the blob path) must give bit-identical results, for an element-wise op, a reducing op with per-tensor output
+    and an optimizer op -- across the threshold (n = 8 / 9), with empty and ragged tensors in the list."""
+    torch.manual_seed(9876 + n)
+    sizes = [0, 1, 5, 4097, 70001, 33, 0, 262144 + 3, 2048][:n] if n > 1 else [70001]
+    pad = [17 + 3 * i for i in range(8)]
+
+    def make(sz):
+        return [torch.randn(s, device="cuda") for s in sz]
+
+    x, extra = make(sizes), make(pad)
+    # scale
+    o1, o2, oe = [torch.empty_like(t) for t in x], [torch.empty_like(t) for t in x], [torch.empty_like(t) for t in extra]
+    f = _flag()
+    amp_C.multi_tensor_scale(8192, f, [x, o1], 0.37)
+    amp_C.multi_tensor_scale(8192, f, [x + extra, o2 + oe], 0.37)
+    assert all(bits_equal(a, b) for a, b in zip(o1, o2))
+    # l2norm with per-tensor output (one tile per chunk, tickets per tensor)
+    g1, p1 = amp_C.multi_tensor_l2norm(4096, f, [x], True)
+    g2, p2 = amp_C.multi_tensor_l2norm(4096, f, [x + extra], True)
+    assert bits_equal(p1, p2[:len(x)])
+    assert max_rel(g1, torch.sqrt((p1.double() ** 2).sum()).float()) < 1e-6
+    # Adam (4 lists)
+    def state():
+        torch.manual_seed(5)
+        return [[t.clone() for t in x], [torch.randn_like(t) for t in x], [torch.randn_like(t) * 0.1 for t in x],
+                [torch.rand_like(t) * 0.01 for t in x]]
+
+    def state_extra():
+        return [[t.clone() for t in extra], [torch.randn_like(t) for t in extra], [torch.zeros_like(t) for t in extra],
+                [torch.zeros_like(t) for t in extra]]
+
+    a, b, e = state(), state(), state_extra()
+    args = (1e-3, 0.9, 0.999, 1e-8, 3, 1, 1, 0.01)
+    amp_C.multi_tensor_adam(8192, f, a, *args)
+    amp_C.multi_tensor_adam(8192, f, [b[d] + e[d] for d in range(4)], *args)
+    for d in range(1, 4):
+        assert all(bits_equal(u, v) for u, v in zip(a[d], b[d]))
+    assert int(f.item()) == 0
