@@ -24,6 +24,10 @@ gradient of the bucket has been produced (:325-362, 612-726).  What differs is u
   * `numels=[...]` (extension) instead of `params`: build the optimizer over bare sizes; parameters are created as
     views of the flat buffer.
 
+As in the reference, every parameter of the groups has optimizer state and takes part in every step (:395-405,
+:977-1115): one that received no gradient is stepped with a zero gradient, i.e. it decays by lr x weight_decay
+(torch.optim.AdamW would skip it).  Keep parameters that must not move out of the optimizer.
+
 `process_group` may be a `distributed_process_group` x `redundant_process_group` grid as in the reference (:62-74): the
 state is sharded over the former and replicated over the latter; gradients are reduce-scattered over the shards'
 group, then all-reduced over the replicas' group (:717-732).  `pipeline_size` and `contiguous_grad_buffer` are

@@ -265,6 +265,56 @@ def grid_2x2(make, rank, device):
     return out
 
 
+def frozen_param_and_lr_schedule(make, rank, device):
+    """Not in the reference's file, but what its class does as a torch.optim.Optimizer: a parameter that never gets a
+    gradient (requires_grad=False) must not block its bucket's reduce-scatter; like the reference -- which creates state
+    for every parameter of the groups (distributed_fused_adam.py:395-405) and updates every fragment of every bucket
+    (:977-1115) -- it is stepped with a ZERO gradient, i.e. it only decays (torch.optim.AdamW would skip it; the
+    comparison below hands AdamW explicit zero gradients).  A scheduler that rewrites param_groups[i]['lr'] between steps
+    must be honoured by the next step (the learning rates live in device memory here), and
+    zero_grad(set_to_none=False) must keep accumulating correctly."""
+    torch.manual_seed(4321 + rank)
+    ref_model = SimpleModel(7, 5).to(device)
+    dist_model = SimpleModel(7, 5).to(device)
+    with torch.no_grad():
+        for rp in ref_model.parameters():
+            buf = rp.float()
+            dist.broadcast(buf, src=0)
+            rp.copy_(buf)
+        for rp, dp in zip(ref_model.parameters(), dist_model.parameters()):
+            dp.copy_(rp)
+    for m in (ref_model, dist_model):
+        m.layers[2].weight.requires_grad_(False)
+        m.layers[3].bias.requires_grad_(False)
+    args = dict(lr=0.05, betas=(0.8, 0.9), eps=1e-3, weight_decay=0.05)
+    rps, dps = list(ref_model.parameters()), list(dist_model.parameters())
+    ref_optim = torch.optim.AdamW([{'params': rps[:5], 'lr': 0.1}, {'params': rps[5:]}], **args)
+    dist_optim = make([{'params': dps[:5], 'lr': 0.1}, {'params': dps[5:]}], bucket_cap_mb=71 / (4 * 1024 * 1024),
+                      device=device, **args)
+    ref_frozen = [ref_model.layers[2].weight, ref_model.layers[3].bias]
+    scheds = [torch.optim.lr_scheduler.StepLR(o, step_size=1, gamma=0.5) for o in (ref_optim, dist_optim)]
+    for step in range(4):
+        ref_optim.zero_grad(set_to_none=False)
+        dist_optim.zero_grad(set_to_none=False)
+        for micro in range(2):
+            x = (torch.rand(3, 5) - 0.5).to(device)
+            dy = (torch.rand(3, 5) - 0.5).to(device)
+            ref_model(x).backward(dy)
+            dist_model(x).backward(dy)
+        _allreduce_avg(ref_model.parameters())
+        for p in ref_frozen:
+            p.grad = torch.zeros_like(p)
+        ref_optim.step()
+        dist_optim.step()
+        for sch in scheds:
+            sch.step()
+        assert dist_optim.param_groups[0]['lr'] == ref_optim.param_groups[0]['lr'] == 0.1 * 0.5 ** (step + 1)
+        for rp, dp in zip(ref_model.parameters(), dist_model.parameters()):
+            torch.testing.assert_close(dp, rp)
+    assert dist_model.layers[2].weight.grad is None and dist_model.layers[3].bias.grad is None
+    return {}
+
+
 CASES = {
     "matches_pytorch": matches_pytorch,
     "matches_pytorch_no_overlap": lambda make, rank, device, **kw: matches_pytorch(
@@ -283,4 +333,5 @@ CASES = {
     "checkpoint": checkpoint,
     "overflow_does_not_stick": overflow_does_not_stick,
     "grid_2x2": grid_2x2,
+    "frozen_param_and_lr_schedule": frozen_param_and_lr_schedule,
 }
