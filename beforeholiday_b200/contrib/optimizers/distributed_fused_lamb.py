@@ -43,7 +43,7 @@ from typing import List, Optional
 import torch
 import torch.distributed as dist
 
-from .flat_sharded_adam import FlatLayout
+from .flat_sharded_adam import FlatLayout, second_communicator
 
 
 class DistributedFusedLAMB(torch.optim.Optimizer):
@@ -167,8 +167,7 @@ class DistributedFusedLAMB(torch.optim.Optimizer):
         self.rs_group = self.ag_group = self.group
         self.ag_stream = None
         if self.world > 1 and self._overlap and self.device.type == "cuda":
-            ranks = list(range(dist.get_world_size())) if self.group is None else dist.get_process_group_ranks(self.group)
-            self.ag_group = dist.new_group(ranks=ranks, backend="nccl")   # all-gathers overlap stage 2 of the next bucket
+            self.ag_group = second_communicator(self.group)   # all-gathers overlap stage 2 of the next bucket
             self.ag_stream = torch.cuda.Stream(self.device)
             self.rs_stream = torch.cuda.Stream(self.device)               # reduce-scatters started from backward hooks
 

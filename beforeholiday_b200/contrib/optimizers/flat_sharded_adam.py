@@ -39,6 +39,25 @@ def _ceil_to(x: int, a: int) -> int:
     return (x + a - 1) // a * a
 
 
+def second_communicator(group, backend="nccl"):
+    """Another communicator over the ranks of `group` (None = the whole job), so that two collectives of one step can
+    be in flight at once.  Collective over the WHOLE job: when `group` is a sub-group (the state sharded over part of
+    the job, the rest holding replicas), every rank creates every such group's communicator, in the same order, as
+    torch.distributed.new_group requires -- creating only one's own would give disjoint groups the same name."""
+    n = dist.get_world_size()
+    ranks = tuple(range(n)) if group is None else tuple(dist.get_process_group_ranks(group))
+    if len(ranks) == n:
+        return dist.new_group(ranks=list(ranks), backend=backend)
+    every = [None] * n
+    dist.all_gather_object(every, ranks)
+    mine = None
+    for rs in sorted(set(every)):
+        g = dist.new_group(ranks=list(rs), backend=backend)
+        if rs == ranks:
+            mine = g
+    return mine
+
+
 @dataclass
 class Fragment:
     """Piece of parameter `param` that lies inside one of this rank's sub-shards."""
@@ -238,9 +257,8 @@ class FlatShardedAdam:
         self.ag_group = self.group
         self.rs_stream = self.ag_stream = None
         if self.world > 1 and self.overlap and self.device.type == "cuda":
-            ranks = list(range(dist.get_world_size())) if self.group is None else dist.get_process_group_ranks(self.group)
             # a second communicator so that all-gathers run concurrently with reduce-scatters
-            self.ag_group = dist.new_group(ranks=ranks, backend="nccl")
+            self.ag_group = second_communicator(self.group)
             self.rs_stream = torch.cuda.Stream(self.device)
             self.ag_stream = torch.cuda.Stream(self.device)
 

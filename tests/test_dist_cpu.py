@@ -375,3 +375,51 @@ def test_dropin_over_bare_sizes_matches_the_engine():
         eng.step()
     assert torch.equal(opt.params_flat, eng.params_flat) and not torch.equal(opt.params_flat[:1000], init[:1000])
     assert opt.state_dict(gather_on_root=False)["state"]["step"] == 2
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# second_communicator: the extra communicator the sharded optimizers open for their all-gathers
+def _second_comm_worker(rank, world, port, outdir):
+    from beforeholiday_b200.contrib.optimizers.flat_sharded_adam import second_communicator
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # whole job
+        g = second_communicator(None, backend="gloo")
+        t = torch.tensor([float(rank + 1)])
+        dist.all_reduce(t, group=g)
+        assert float(t) == world * (world + 1) / 2
+        # state sharded over disjoint halves of the job (the distributed x redundant grid): each rank asks for a second
+        # communicator over ITS half; every rank must take part in creating both
+        halves = [dist.new_group([0, 1]), dist.new_group([2, 3])]
+        mine = halves[rank // 2]
+        g2 = second_communicator(mine, backend="gloo")
+        assert dist.get_process_group_ranks(g2) == dist.get_process_group_ranks(mine)
+        t = torch.tensor([float(rank + 1)])
+        dist.all_reduce(t, group=g2)
+        assert float(t) == (3.0 if rank < 2 else 7.0)
+        # both communicators of a half are usable side by side
+        a, b = torch.ones(1), torch.ones(1)
+        w1 = dist.all_reduce(a, group=mine, async_op=True)
+        w2 = dist.all_reduce(b, group=g2, async_op=True)
+        w1.wait()
+        w2.wait()
+        assert float(a) == float(b) == 2.0
+        open(os.path.join(outdir, f"ok{rank}"), "w").close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_second_communicator_over_sub_groups_world4(tmp_path):
+    world = 4
+    ctx = mp.get_context("spawn")
+    port = _free_port()
+    procs = [ctx.Process(target=_second_comm_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        assert p.exitcode == 0
+    assert all((tmp_path / f"ok{r}").exists() for r in range(world))
